@@ -1,0 +1,136 @@
+/*
+ * b200_sharded.h -- C ABI of libb200sl.so, the B200 (sm_100a) per-shard compute
+ * library behind the sharded matmul / Dense / FFN / attention layers that the
+ * entrpn/learning-jax-sharding case scripts run under jax.jit.
+ *
+ * Every entry point is what an XLA FFI custom-call handler (or a ctypes / cffi
+ * binding) for that layer would call once per device with that device's shard
+ * buffers -- INTEGRATION.md shows both bindings.  Conventions:
+ *   - all buffers are DEVICE pointers owned by the caller; results are
+ *     pre-allocated by the caller; nothing is retained, freed or resized here;
+ *   - calls only ENQUEUE work on `stream` (a cudaStream_t passed as void*; NULL =
+ *     legacy default stream) of the CURRENT device and never synchronise it;
+ *   - no exceptions cross the boundary: the return value is a b200_status and
+ *     b200_last_error() returns a thread-local message for the last failure;
+ *   - no torch / C++ types in any signature.
+ * The reference has no native code; each comment cites the reference Python call
+ * site (file:line under the upstream repo) whose per-device lowering the entry
+ * point replaces.
+ */
+#ifndef B200_SHARDED_H_
+#define B200_SHARDED_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_VERSION 100 /* major*10000 + minor*100 + patch */
+
+typedef enum {
+  B200_OK = 0,
+  B200_ERR_INVALID_ARGUMENT = 1, /* shape / alignment / enum out of range            */
+  B200_ERR_CUDA = 2,             /* a CUDA runtime or driver call failed              */
+  B200_ERR_UNSUPPORTED = 3       /* valid request this build has no kernel for        */
+} b200_status;
+
+typedef enum { B200_BF16 = 0, B200_F32 = 1 } b200_dtype;
+
+/* Epilogue fused into the GEMM's TMEM->global path.  Rounding follows two chained
+ * bf16 flax.linen.Dense layers: bf16(acc), then bf16(+bias), then bf16(act(.)). */
+typedef enum {
+  B200_EPI_NONE = 0,
+  B200_EPI_BIAS = 1,
+  B200_EPI_BIAS_RELU = 2,
+  B200_EPI_BIAS_GELU_TANH = 3,
+  B200_EPI_RELU = 4,
+  B200_EPI_GELU_TANH = 5
+} b200_epilogue;
+
+/* Layout of the B operand of b200_gemm_bf16. */
+typedef enum {
+  B200_B_KN = 0, /* B is [K,N] row-major: a flax Dense kernel (in_features, out_features) */
+  B200_B_NK = 1  /* B is [N,K] row-major: C = A . B^T (e.g. Q.K^T, pre-transposed weights) */
+} b200_b_layout;
+
+/* Library version (B200_VERSION of the build). */
+int b200_version(void);
+/* Message for the last non-OK status returned on this host thread ("" if none). */
+const char* b200_last_error(void);
+/* Number of kernels this library has launched in this process (all threads). */
+int64_t b200_launch_count(void);
+
+/*
+ * C[M,N] = epilogue(A[M,K] . B + bias), bf16 inputs, f32 accumulation in TMEM
+ * (tcgen05.mma), output bf16 or f32.  A row-major with row stride lda (elements),
+ * B per b_layout with row stride ldb, C row-major with row stride ldc.
+ * Requirements: K % 8 == 0, N % 8 == 0, lda/ldb/ldc % 8 == 0, 16-byte aligned bases.
+ * bias: bf16[N] or NULL (required for the *_BIAS_* epilogues).
+ * Replaces the per-device lowering of flax nn.Dense(dtype=bf16)
+ *   (case6_attention.py:61-90,96-99,139; case5_attention_dense.py:59-67)
+ * and of each half of the FFN  y = act(x.Win).Wout  (case6_attention.py:36-40;
+ * column-parallel half case4_gspmd_ff.py:46-52, row-parallel half case1a.py:24-49).
+ */
+int b200_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, int b_layout, const void* bias,
+                   void* C, int64_t ldc, int out_dtype, int M, int N, int K, int epilogue, void* stream);
+
+/*
+ * Batched true-fp32 GEMM (FFMA, no TF32): for b in [0,batch):
+ *   C_b[M,N] = A_b[M,K] . B_b[K,N], all row-major, element strides lda/ldb/ldc
+ *   between rows and strideA/strideB/strideC between batch items.
+ * If accumulate != 0 the product is added to C (used to sum K-partials locally).
+ * Replaces the per-device dot of jax.lax.dot on sharded operands
+ *   (case1a.py:49; case1b.py:47; case2.py:44; case3_fully_sharded.py:46;
+ *    case4_gspmd_ff.py:52) and jnp.einsum("ABC,ACD->ABD") (case4_gspmd_ff.py:30).
+ */
+int b200_gemm_f32(const float* A, int64_t lda, int64_t strideA, const float* B, int64_t ldb, int64_t strideB,
+                  float* C, int64_t ldc, int64_t strideC, int batch, int M, int N, int K, int accumulate,
+                  void* stream);
+
+/*
+ * Multi-head attention core, forward:  O = softmax(scale * Q.K^T [+ causal mask]) . V
+ * Q: [B,Sq,H,D], K,V: [B,Sk,H,D], O: [B,Sq,H,D]; bf16; head dim innermost, heads
+ * second-innermost (the reference's "b s n h" layout, so the (b,S,N*D) projection
+ * output is consumed without a transpose).  Row strides (elements) are given per
+ * tensor as (batch, seq, head); the D elements of a head are contiguous.
+ * Scores and softmax are f32, P is rounded to bf16 before P.V, O is bf16 --
+ * the order of case6_attention.py:121-135 (online softmax, never materialises S).
+ * causal != 0 masks keys t > f + (Sk - Sq) (the BASELINE.json case6 config; the
+ * reference itself has no mask, case6_attention.py:125-127).  D in {64, 128}.
+ */
+int b200_attention_fwd(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
+                       int64_t q_stride_b, int64_t q_stride_s, int64_t q_stride_h, int64_t k_stride_b,
+                       int64_t k_stride_s, int64_t k_stride_h, int64_t v_stride_b, int64_t v_stride_s,
+                       int64_t v_stride_h, int64_t o_stride_b, int64_t o_stride_s, int64_t o_stride_h, float scale,
+                       int causal, void* stream);
+
+/*
+ * One device's share of the feed-forward block  y = act(x.W1 + b1).W2 (+ b2):
+ * x [T,d_model] bf16, W1 [d_model,F] ([K,N] row-major), b1 [F] or NULL,
+ * W2 [F,d_model], b2 [d_model] or NULL, h [T,F] bf16 caller-provided workspace,
+ * y [T,d_model] bf16 (or f32 when y_dtype = B200_F32, for partial sums that a
+ * row-parallel reduction will add).  F is the LOCAL d_ff (d_ff / model-axis size):
+ * W1 column-parallel, W2 row-parallel; with F < d_ff the caller must all-reduce
+ * or reduce-scatter y over the 'model' axis and pass b2 on one rank only.
+ * act: B200_EPI_BIAS_RELU / B200_EPI_BIAS_GELU_TANH / B200_EPI_RELU / B200_EPI_GELU_TANH.
+ * Reference: the FFN comment at case6_attention.py:36-40 (= case5_attention_dense.py:35-39).
+ */
+int b200_ffn_fwd(const void* x, const void* W1, const void* b1, const void* W2, const void* b2, void* h, void* y,
+                 int y_dtype, int T, int d_model, int F, int act, void* stream);
+
+/* dst[i] = bf16(src[i]) -- the per-call f32->bf16 parameter/activation cast flax
+ * promote_dtype performs inside nn.Dense (case6_attention.py:61-90). n elements. */
+int b200_cast_f32_to_bf16(const float* src, void* dst, int64_t n, void* stream);
+/* dst[i] = f32(src[i]), n elements. */
+int b200_cast_bf16_to_f32(const void* src, float* dst, int64_t n, void* stream);
+/* dst[i] = bf16(sum_r src_r[i]) over `nsrc` f32 partial buffers laid out back to back
+ * with stride `src_stride` elements; optional bf16 bias[cols] added per row.
+ * Finishes a row-parallel reduction whose partials were exchanged in f32. */
+int b200_sum_partials_to_bf16(const float* src, int64_t src_stride, int nsrc, const void* bias, int64_t cols,
+                              void* dst, int64_t n, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_SHARDED_H_ */

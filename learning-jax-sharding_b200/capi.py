@@ -1,0 +1,245 @@
+"""ctypes binding of libb200sl.so (include/b200_sharded.h).
+
+The library is the product: there is NO CPU or eager-PyTorch fallback.  If the shared
+object has not been built (``learning-jax-sharding_b200/build.sh`` or
+``__graft_entry__.build()``), or a tensor is not a CUDA tensor, the wrappers raise.
+
+Tensors are only containers here: each wrapper passes ``tensor.data_ptr()`` and the
+current torch CUDA stream to the ``extern "C"`` entry point, which enqueues its kernels
+on that stream and returns immediately.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200sl.so")
+
+# enums of include/b200_sharded.h
+BF16, F32 = 0, 1
+EPI_NONE, EPI_BIAS, EPI_BIAS_RELU, EPI_BIAS_GELU_TANH, EPI_RELU, EPI_GELU_TANH = range(6)
+B_KN, B_NK = 0, 1
+
+EXPORTED_SYMBOLS = (
+    "b200_version",
+    "b200_last_error",
+    "b200_launch_count",
+    "b200_gemm_bf16",
+    "b200_gemm_f32",
+    "b200_attention_fwd",
+    "b200_ffn_fwd",
+    "b200_cast_f32_to_bf16",
+    "b200_cast_bf16_to_f32",
+    "b200_sum_partials_to_bf16",
+)
+
+
+class B200Error(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load():
+    """Load libb200sl.so once; raise loudly if it is missing (no fallback path exists)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise B200Error(
+            f"{LIB_PATH} is missing: build it with learning-jax-sharding_b200/build.sh "
+            "(or __graft_entry__.build()). There is no CPU/PyTorch fallback for the sharded layers."
+        )
+    lib = ctypes.CDLL(LIB_PATH)
+    i32, i64, vp, f32 = ctypes.c_int, ctypes.c_int64, ctypes.c_void_p, ctypes.c_float
+    lib.b200_version.restype = i32
+    lib.b200_last_error.restype = ctypes.c_char_p
+    lib.b200_launch_count.restype = i64
+    lib.b200_gemm_bf16.argtypes = [vp, i64, vp, i64, i32, vp, vp, i64, i32, i32, i32, i32, i32, vp]
+    lib.b200_gemm_f32.argtypes = [vp, i64, i64, vp, i64, i64, vp, i64, i64, i32, i32, i32, i32, i32, vp]
+    lib.b200_attention_fwd.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32] + [i64] * 12 + [f32, i32, vp]
+    lib.b200_ffn_fwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp]
+    lib.b200_cast_f32_to_bf16.argtypes = [vp, vp, i64, vp]
+    lib.b200_cast_bf16_to_f32.argtypes = [vp, vp, i64, vp]
+    lib.b200_sum_partials_to_bf16.argtypes = [vp, i64, i32, vp, i64, vp, i64, vp]
+    lib.b200_gemm_set_tuning.argtypes = [i32, i32]
+    for name in EXPORTED_SYMBOLS[3:] + ("b200_gemm_set_tuning",):
+        getattr(lib, name).restype = i32
+    _lib = lib
+    return lib
+
+
+def _check(rc: int, what: str):
+    if rc != 0:
+        msg = load().b200_last_error().decode("utf-8", "replace")
+        raise B200Error(f"{what} failed (status {rc}): {msg}")
+
+
+def _ptr(t):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _stream(t: torch.Tensor):
+    return ctypes.c_void_p(torch.cuda.current_stream(t.device).cuda_stream)
+
+
+def _require_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise B200Error(
+                "b200 sharded layers run on CUDA tensors only (got a "
+                f"{t.device} tensor); there is no CPU fallback"
+            )
+
+
+def launch_count() -> int:
+    return int(load().b200_launch_count())
+
+
+def set_gemm_tuning(cta_group: int = 0, block_n: int = 0):
+    """Force the GEMM tile configuration (0 = library heuristic). For tests and tuning runs."""
+    _check(load().b200_gemm_set_tuning(cta_group, block_n), "b200_gemm_set_tuning")
+
+
+def gemm_bf16(a, b, *, b_layout=B_KN, bias=None, epilogue=EPI_NONE, out=None, out_dtype=torch.bfloat16):
+    """out[M,N] = epilogue(a[M,K] @ B + bias). ``b`` is [K,N] (B_KN, a Dense kernel) or [N,K] (B_NK).
+
+    a, b, out may be row-strided views (last dim contiguous)."""
+    _require_cuda(a, b, bias, out)
+    if a.dtype != torch.bfloat16 or b.dtype != torch.bfloat16:
+        raise B200Error("gemm_bf16 takes bf16 operands")
+    if a.dim() != 2 or b.dim() != 2 or a.stride(1) != 1 or b.stride(1) != 1:
+        raise B200Error("gemm_bf16 takes 2-D operands with a contiguous last dim")
+    M, K = a.shape
+    if b_layout == B_KN:
+        Kb, N = b.shape
+    else:
+        N, Kb = b.shape
+    if Kb != K:
+        raise B200Error(f"gemm_bf16: contraction mismatch {tuple(a.shape)} x {tuple(b.shape)} (layout {b_layout})")
+    if out is None:
+        out = torch.empty((M, N), dtype=out_dtype, device=a.device)
+    if out.shape != (M, N) or out.stride(1) != 1 or out.dtype not in (torch.bfloat16, torch.float32):
+        raise B200Error("gemm_bf16: bad output tensor")
+    if bias is not None and (bias.dtype != torch.bfloat16 or bias.numel() != N or not bias.is_contiguous()):
+        raise B200Error("gemm_bf16: bias must be a contiguous bf16 vector of length N")
+    with torch.cuda.device(a.device):
+        rc = load().b200_gemm_bf16(
+            _ptr(a), a.stride(0), _ptr(b), b.stride(0), b_layout, _ptr(bias), _ptr(out), out.stride(0),
+            F32 if out.dtype == torch.float32 else BF16, M, N, K, epilogue, _stream(a))
+    _check(rc, "b200_gemm_bf16")
+    return out
+
+
+def gemm_f32(a, b, *, out=None, accumulate=False):
+    """True-fp32 (batched) matmul: a [.., M, K] @ b [.., K, N]; leading batch dim optional."""
+    _require_cuda(a, b, out)
+    if a.dtype != torch.float32 or b.dtype != torch.float32:
+        raise B200Error("gemm_f32 takes fp32 operands")
+    batched = a.dim() == 3
+    a3 = a if batched else a.unsqueeze(0)
+    b3 = b if b.dim() == 3 else b.unsqueeze(0)
+    if a3.dim() != 3 or b3.dim() != 3 or a3.shape[0] != b3.shape[0] or a3.shape[2] != b3.shape[1]:
+        raise B200Error(f"gemm_f32: shape mismatch {tuple(a.shape)} x {tuple(b.shape)}")
+    if a3.stride(2) != 1 or b3.stride(2) != 1:
+        raise B200Error("gemm_f32 takes operands with a contiguous last dim")
+    Bt, M, K = a3.shape
+    N = b3.shape[2]
+    if out is None:
+        if accumulate:
+            raise B200Error("gemm_f32: accumulate needs an output tensor")
+        out = torch.empty((Bt, M, N) if batched else (M, N), dtype=torch.float32, device=a.device)
+    o3 = out if out.dim() == 3 else out.unsqueeze(0)
+    if o3.shape != (Bt, M, N) or o3.stride(2) != 1 or out.dtype != torch.float32:
+        raise B200Error("gemm_f32: bad output tensor")
+    with torch.cuda.device(a.device):
+        rc = load().b200_gemm_f32(
+            _ptr(a3), a3.stride(1), a3.stride(0), _ptr(b3), b3.stride(1), b3.stride(0), _ptr(o3), o3.stride(1),
+            o3.stride(0), Bt, M, N, K, int(bool(accumulate)), _stream(a))
+    _check(rc, "b200_gemm_f32")
+    return out
+
+
+def attention_fwd(q, k, v, *, scale=None, causal=False, out=None):
+    """softmax(scale * q k^T [+causal]) v with q [B,Sq,H,D], k/v [B,Sk,H,D] bf16 (b s n h layout)."""
+    _require_cuda(q, k, v, out)
+    for t in (q, k, v):
+        if t.dtype != torch.bfloat16 or t.dim() != 4 or t.stride(3) != 1:
+            raise B200Error("attention_fwd takes 4-D bf16 tensors [B,S,H,D] with contiguous D")
+    B, Sq, H, D = q.shape
+    Sk = k.shape[1]
+    if k.shape != (B, Sk, H, D) or v.shape != (B, Sk, H, D):
+        raise B200Error(f"attention_fwd: shape mismatch q{tuple(q.shape)} k{tuple(k.shape)} v{tuple(v.shape)}")
+    if out is None:
+        out = torch.empty((B, Sq, H, D), dtype=torch.bfloat16, device=q.device)
+    if scale is None:
+        scale = D ** -0.5
+    with torch.cuda.device(q.device):
+        rc = load().b200_attention_fwd(
+            _ptr(q), _ptr(k), _ptr(v), _ptr(out), B, Sq, Sk, H, D,
+            q.stride(0), q.stride(1), q.stride(2), k.stride(0), k.stride(1), k.stride(2),
+            v.stride(0), v.stride(1), v.stride(2), out.stride(0), out.stride(1), out.stride(2),
+            float(scale), int(bool(causal)), _stream(q))
+    _check(rc, "b200_attention_fwd")
+    return out
+
+
+def ffn_fwd(x, w1, b1, w2, b2, *, act=EPI_BIAS_GELU_TANH, h=None, out=None, out_dtype=torch.bfloat16):
+    """y = act(x @ w1 + b1) @ w2 (+ b2) for one device's shard (w1 [d_model,F], w2 [F,d_model])."""
+    _require_cuda(x, w1, b1, w2, b2, h, out)
+    T, d_model = x.shape
+    F = w1.shape[1]
+    for t in (x, w1, w2):
+        if t.dtype != torch.bfloat16 or not t.is_contiguous():
+            raise B200Error("ffn_fwd takes contiguous bf16 tensors")
+    if w1.shape != (d_model, F) or w2.shape != (F, d_model):
+        raise B200Error("ffn_fwd: weight shapes do not match x")
+    if h is None:
+        h = torch.empty((T, F), dtype=torch.bfloat16, device=x.device)
+    if out is None:
+        out = torch.empty((T, d_model), dtype=out_dtype, device=x.device)
+    with torch.cuda.device(x.device):
+        rc = load().b200_ffn_fwd(
+            _ptr(x), _ptr(w1), _ptr(b1), _ptr(w2), _ptr(b2), _ptr(h), _ptr(out),
+            F32 if out.dtype == torch.float32 else BF16, T, d_model, F, act, _stream(x))
+    _check(rc, "b200_ffn_fwd")
+    return out
+
+
+def cast_f32_to_bf16(src, out=None):
+    _require_cuda(src, out)
+    src = src.contiguous()
+    if out is None:
+        out = torch.empty(src.shape, dtype=torch.bfloat16, device=src.device)
+    with torch.cuda.device(src.device):
+        rc = load().b200_cast_f32_to_bf16(_ptr(src), _ptr(out), src.numel(), _stream(src))
+    _check(rc, "b200_cast_f32_to_bf16")
+    return out
+
+
+def cast_bf16_to_f32(src, out=None):
+    _require_cuda(src, out)
+    src = src.contiguous()
+    if out is None:
+        out = torch.empty(src.shape, dtype=torch.float32, device=src.device)
+    with torch.cuda.device(src.device):
+        rc = load().b200_cast_bf16_to_f32(_ptr(src), _ptr(out), src.numel(), _stream(src))
+    _check(rc, "b200_cast_bf16_to_f32")
+    return out
+
+
+def sum_partials_to_bf16(partials, bias=None, out=None):
+    """partials: f32 [R, rows, cols] (contiguous) -> bf16 [rows, cols] = bf16(sum_r) (+ bias)."""
+    _require_cuda(partials, bias, out)
+    R, rows, cols = partials.shape
+    if out is None:
+        out = torch.empty((rows, cols), dtype=torch.bfloat16, device=partials.device)
+    with torch.cuda.device(partials.device):
+        rc = load().b200_sum_partials_to_bf16(
+            _ptr(partials), rows * cols, R, _ptr(bias), cols, _ptr(out), rows * cols, _stream(partials))
+    _check(rc, "b200_sum_partials_to_bf16")
+    return out

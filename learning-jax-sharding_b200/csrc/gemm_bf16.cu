@@ -1,0 +1,437 @@
+// bf16 GEMM with fused epilogue for sm_100a: C = epi(A . B + bias).
+//
+// Persistent, warp-specialised kernel; one CTA (or one CTA pair, cta_group::2) per SM:
+//   warp 0      TMA producer   global -> 128B-swizzled smem ring (mbarrier full/empty)
+//   warp 1      MMA issuer     one thread issues tcgen05.mma, accumulators live in TMEM
+//   warp 2      TMEM allocator (512 columns = two accumulator stages of up to 256 columns)
+//   warps 4..7  epilogue       tcgen05.ld TMEM -> registers -> bias / activation -> global
+// The two accumulator stages let the epilogue of tile i overlap the main loop of tile i+1.
+//
+// This is the per-device compute behind flax nn.Dense(dtype=bf16) (reference
+// case6_attention.py:61-90,96-99,139; case5_attention_dense.py:59-67) and both halves
+// of the FFN (case6_attention.py:36-40).  B is taken in the layout the reference keeps
+// Dense kernels in, (in_features, out_features) row-major = "[K,N]", which tcgen05 reads
+// as an MN-major operand; the [N,K] layout (K-major) is also supported.
+#include <cuda.h>
+
+#include "host_common.h"
+#include "sm100_ptx.cuh"
+
+namespace b200 {
+
+constexpr int kBM = 128;        // rows of C per CTA (TMEM lanes)
+constexpr int kBK = 64;         // K elements per pipeline stage = one 128-byte swizzle row
+constexpr int kUmmaK = 16;      // K per tcgen05.mma for 16-bit inputs
+constexpr int kGemmThreads = 256;
+constexpr int kGroupM = 8;      // tile rasterisation: kGroupM row-blocks share B panels in L2
+
+template <int BN, int G>
+struct GemmCfg {
+  static constexpr int kBNcta = BN / G;                         // B rows/cols loaded by one CTA
+  static constexpr int kABytes = kBM * kBK * 2;                 // 16 KB
+  static constexpr int kBBytes = kBNcta * kBK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kSmemBudget = 227 * 1024 - 1024 /*align slack*/ - 256 /*barriers*/;
+  static constexpr int kStages = kSmemBudget / kStageBytes > 8 ? 8 : kSmemBudget / kStageBytes;
+  static constexpr int kAccStages = 2;
+  static constexpr int kTmemCols = 512;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+struct GemmParams {
+  void* C;
+  const __nv_bfloat16* bias;
+  int M, N, K;
+  int64_t ldc;
+  int epilogue;
+  int out_f32;
+  int tiles_m, tiles_n;
+};
+
+__device__ __forceinline__ float gelu_tanh_f(float x) {
+  // 0.5 x (1 + tanh( sqrt(2/pi) (x + 0.044715 x^3) ))  -- jax.nn.gelu(approximate=True)
+  const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+  float u = k0 * (x + k1 * x * x * x);
+  return 0.5f * x * (1.0f + tanh_approx(u));
+}
+
+__device__ __forceinline__ float apply_epilogue(float acc, float bias, int epi, bool out_f32) {
+  if (out_f32 && epi == B200_EPI_NONE) return acc;   // raw f32 partial sums (row-parallel reductions)
+  float v = bf16_round(acc);                          // Dense: result is cast to bf16 first ...
+  if (epi == B200_EPI_BIAS || epi == B200_EPI_BIAS_RELU || epi == B200_EPI_BIAS_GELU_TANH)
+    v = bf16_round(v + bias);                         // ... then the bf16 bias is added in bf16
+  if (epi == B200_EPI_BIAS_RELU || epi == B200_EPI_RELU) v = fmaxf(v, 0.0f);
+  if (epi == B200_EPI_BIAS_GELU_TANH || epi == B200_EPI_GELU_TANH) v = gelu_tanh_f(v);
+  return v;
+}
+
+__device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, int& m_blk, int& n_blk) {
+  const int per_group = kGroupM * tiles_n;
+  const int group = tile / per_group;
+  const int first_m = group * kGroupM;
+  const int gsize = min(tiles_m - first_m, kGroupM);
+  const int in_group = tile - group * per_group;
+  m_blk = first_m + in_group % gsize;
+  n_blk = in_group / gsize;
+}
+
+template <int BN, int G, bool kBKmajor>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 const GemmParams p) {
+  using Cfg = GemmCfg<BN, G>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + Cfg::kStages;
+  uint64_t* tmem_full_bar = bars + 2 * Cfg::kStages;
+  uint64_t* tmem_empty_bar = tmem_full_bar + Cfg::kAccStages;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty_bar + Cfg::kAccStages);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  uint32_t cta_rank = 0;
+  if (G == 2) asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta_rank));
+  const bool leader = (cta_rank == 0);
+
+  const int num_tiles = p.tiles_m * p.tiles_n;
+  const int num_workers = gridDim.x / G;       // CTAs (G=1) or CTA pairs (G=2)
+  const int worker = blockIdx.x / G;
+  const int num_kb = (p.K + kBK - 1) / kBK;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < Cfg::kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int a = 0; a < Cfg::kAccStages; ++a) {
+      mbar_init(&tmem_full_bar[a], 1);
+      mbar_init(&tmem_empty_bar[a], 4 * G);    // one arrival per epilogue warp of every CTA of the group
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    if (G == 1) tmem_alloc<Cfg::kTmemCols>(tmem_ptr_smem);
+    else tmem_alloc_cg2<Cfg::kTmemCols>(tmem_ptr_smem);
+  }
+  tc_fence_before();
+  if (G == 2) {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  } else {
+    __syncthreads();
+  }
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 0 && lane == 0) {
+    // ===================== TMA producer =====================
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = worker; tile < num_tiles; tile += num_workers) {
+      int m_blk, n_blk;
+      tile_coords(tile, p.tiles_m, p.tiles_n, m_blk, n_blk);
+      const int m0 = (m_blk * G + cta_rank) * kBM;
+      const int n0 = n_blk * BN + cta_rank * Cfg::kBNcta;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t* sa = smem + stage * Cfg::kStageBytes;
+        uint8_t* sb = sa + Cfg::kABytes;
+        const int k0 = kb * kBK;
+        if (G == 1) {
+          mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+          tma_load_2d(sa, &tmA, &full_bar[stage], k0, m0);
+          if (kBKmajor) {
+            tma_load_2d(sb, &tmB, &full_bar[stage], k0, n0);
+          } else {
+#pragma unroll
+            for (int c = 0; c < Cfg::kBNcta / 64; ++c)
+              tma_load_2d(sb + c * (kBK * 128), &tmB, &full_bar[stage], n0 + c * 64, k0);
+          }
+        } else {
+          // both CTAs' bytes complete on the leader's barrier
+          if (leader) mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes * 2);
+          tma_load_2d_cg2(sa, &tmA, &full_bar[stage], k0, m0);
+          if (kBKmajor) {
+            tma_load_2d_cg2(sb, &tmB, &full_bar[stage], k0, n0);
+          } else {
+#pragma unroll
+            for (int c = 0; c < Cfg::kBNcta / 64; ++c)
+              tma_load_2d_cg2(sb + c * (kBK * 128), &tmB, &full_bar[stage], n0 + c * 64, k0);
+          }
+        }
+        if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1 && lane == 0 && leader) {
+    // ===================== MMA issuer (leader CTA only) =====================
+    constexpr uint32_t idesc = make_idesc_bf16(kBM * G, BN, false, !kBKmajor);
+    int stage = 0;
+    uint32_t phase = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = worker; tile < num_tiles; tile += num_workers) {
+      mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1);
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + acc * BN;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
+        const uint32_t sb = sa + Cfg::kABytes;
+#pragma unroll
+        for (int k = 0; k < kBK / kUmmaK; ++k) {
+          // A: K-major, 32 bytes of K per MMA inside the 128-byte swizzle row
+          const uint64_t da = make_smem_desc_sw128(sa + k * (kUmmaK * 2), 16, 1024);
+          // B K-major: same; B MN-major ([K,N] row-major): 16 K-rows of 128 B per MMA,
+          // 64-column chunks kBK*128 bytes apart
+          const uint64_t db = kBKmajor ? make_smem_desc_sw128(sb + k * (kUmmaK * 2), 16, 1024)
+                                       : make_smem_desc_sw128(sb + k * (kUmmaK * 128), kBK * 128, 1024);
+          const uint32_t accum = (kb > 0 || k > 0) ? 1u : 0u;
+          if (G == 1) mma_bf16_ss(tmem_d, da, db, idesc, accum);
+          else mma_bf16_ss_cg2(tmem_d, da, db, idesc, accum);
+        }
+        // frees this smem stage (in both CTAs) once the MMAs above have read it
+        if (G == 1) mma_commit(&empty_bar[stage]);
+        else mma_commit_cg2(&empty_bar[stage], 0x3);
+        if (kb == num_kb - 1) {
+          if (G == 1) mma_commit(&tmem_full_bar[acc]);
+          else mma_commit_cg2(&tmem_full_bar[acc], 0x3);
+        }
+        if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+      }
+      if (++acc == Cfg::kAccStages) { acc = 0; acc_phase ^= 1; }
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue =====================
+    const int q = warp & 3;                    // TMEM lane quadrant this warp may read
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    const bool out_f32 = p.out_f32 != 0;
+    const bool has_bias = p.bias != nullptr;
+    for (int tile = worker; tile < num_tiles; tile += num_workers) {
+      int m_blk, n_blk;
+      tile_coords(tile, p.tiles_m, p.tiles_n, m_blk, n_blk);
+      const int row = (m_blk * G + cta_rank) * kBM + q * 32 + lane;
+      const int n0 = n_blk * BN;
+      mbar_wait(&tmem_full_bar[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(taddr + c * 32, r);
+        tmem_wait_ld();
+        const int col0 = n0 + c * 32;
+        if (row < p.M && col0 < p.N) {
+          if (out_f32) {
+            float* dst = reinterpret_cast<float*>(p.C) + static_cast<int64_t>(row) * p.ldc + col0;
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              if (col0 + j < p.N) {
+                float4 v;
+                float b0 = 0.f, b1 = 0.f, b2 = 0.f, b3 = 0.f;
+                if (has_bias) {
+                  b0 = __bfloat162float(p.bias[col0 + j]);
+                  b1 = __bfloat162float(p.bias[col0 + j + 1]);
+                  b2 = __bfloat162float(p.bias[col0 + j + 2]);
+                  b3 = __bfloat162float(p.bias[col0 + j + 3]);
+                }
+                v.x = apply_epilogue(__uint_as_float(r[j]), b0, p.epilogue, true);
+                v.y = apply_epilogue(__uint_as_float(r[j + 1]), b1, p.epilogue, true);
+                v.z = apply_epilogue(__uint_as_float(r[j + 2]), b2, p.epilogue, true);
+                v.w = apply_epilogue(__uint_as_float(r[j + 3]), b3, p.epilogue, true);
+                *reinterpret_cast<float4*>(dst + j) = v;
+              }
+            }
+          } else {
+            __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.C) + static_cast<int64_t>(row) * p.ldc + col0;
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              if (col0 + j < p.N) {     // N % 8 == 0: a group of 8 columns is all in or all out
+                float bv[8];
+                if (has_bias) {
+                  uint4 braw = *reinterpret_cast<const uint4*>(p.bias + col0 + j);
+                  const __nv_bfloat162* b2 = reinterpret_cast<const __nv_bfloat162*>(&braw);
+#pragma unroll
+                  for (int t = 0; t < 4; ++t) {
+                    float2 f = __bfloat1622float2(b2[t]);
+                    bv[2 * t] = f.x;
+                    bv[2 * t + 1] = f.y;
+                  }
+                } else {
+#pragma unroll
+                  for (int t = 0; t < 8; ++t) bv[t] = 0.f;
+                }
+                uint4 o;
+                o.x = pack_bf16x2(apply_epilogue(__uint_as_float(r[j + 0]), bv[0], p.epilogue, false),
+                                  apply_epilogue(__uint_as_float(r[j + 1]), bv[1], p.epilogue, false));
+                o.y = pack_bf16x2(apply_epilogue(__uint_as_float(r[j + 2]), bv[2], p.epilogue, false),
+                                  apply_epilogue(__uint_as_float(r[j + 3]), bv[3], p.epilogue, false));
+                o.z = pack_bf16x2(apply_epilogue(__uint_as_float(r[j + 4]), bv[4], p.epilogue, false),
+                                  apply_epilogue(__uint_as_float(r[j + 5]), bv[5], p.epilogue, false));
+                o.w = pack_bf16x2(apply_epilogue(__uint_as_float(r[j + 6]), bv[6], p.epilogue, false),
+                                  apply_epilogue(__uint_as_float(r[j + 7]), bv[7], p.epilogue, false));
+                *reinterpret_cast<uint4*>(dst + j) = o;
+              }
+            }
+          }
+        }
+      }
+      // accumulator stage drained: hand it back to the MMA issuer (in the leader CTA)
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if (G == 1) mbar_arrive(&tmem_empty_bar[acc]);
+        else mbar_arrive_cluster(&tmem_empty_bar[acc], 0);
+      }
+      if (++acc == Cfg::kAccStages) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+
+  // ===================== teardown =====================
+  __syncwarp();
+  tc_fence_before();
+  if (G == 2) {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  } else {
+    __syncthreads();
+  }
+  if (warp == 2) {
+    tc_fence_after();
+    if (G == 1) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+    else tmem_dealloc_cg2<Cfg::kTmemCols>(tmem_base);
+  }
+}
+
+// ------------------------------------------------------------------ host side
+static int g_force_cta_group = 0;   // 0 = heuristic; 1 / 2 force (set through b200_gemm_set_tuning)
+static int g_force_bn = 0;
+
+template <int BN, int G, bool kBKmajor>
+static int launch_gemm(const void* A, int64_t lda, const void* B, int64_t ldb, const GemmParams& p0,
+                       cudaStream_t stream) {
+  using Cfg = GemmCfg<BN, G>;
+  GemmParams p = p0;
+  p.tiles_m = (p.M + kBM * G - 1) / (kBM * G);
+  p.tiles_n = (p.N + BN - 1) / BN;
+  CUtensorMap tmA, tmB;
+  {
+    uint64_t dims[2] = {static_cast<uint64_t>(p.K), static_cast<uint64_t>(p.M)};
+    uint64_t strides[2] = {0, static_cast<uint64_t>(lda) * 2};
+    uint32_t box[2] = {kBK, kBM};
+    int rc = make_tensor_map(&tmA, A, 2, 2, dims, strides, box, 3);
+    if (rc != B200_OK) return rc;
+  }
+  if (kBKmajor) {
+    uint64_t dims[2] = {static_cast<uint64_t>(p.K), static_cast<uint64_t>(p.N)};
+    uint64_t strides[2] = {0, static_cast<uint64_t>(ldb) * 2};
+    uint32_t box[2] = {kBK, static_cast<uint32_t>(Cfg::kBNcta)};
+    int rc = make_tensor_map(&tmB, B, 2, 2, dims, strides, box, 3);
+    if (rc != B200_OK) return rc;
+  } else {
+    uint64_t dims[2] = {static_cast<uint64_t>(p.N), static_cast<uint64_t>(p.K)};
+    uint64_t strides[2] = {0, static_cast<uint64_t>(ldb) * 2};
+    uint32_t box[2] = {64, kBK};
+    int rc = make_tensor_map(&tmB, B, 2, 2, dims, strides, box, 3);
+    if (rc != B200_OK) return rc;
+  }
+  auto kern = gemm_bf16_kernel<BN, G, kBKmajor>;
+  B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+  const int sms = num_sms();
+  const int tiles = p.tiles_m * p.tiles_n;
+  int workers = sms / G;
+  if (tiles < workers) workers = tiles;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(workers * G);
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attrs[1];
+  attrs[0].id = cudaLaunchAttributeClusterDimension;
+  attrs[0].val.clusterDim.x = G;
+  attrs[0].val.clusterDim.y = 1;
+  attrs[0].val.clusterDim.z = 1;
+  cfg.attrs = attrs;
+  cfg.numAttrs = 1;
+  B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, p));
+  launch_counter().fetch_add(1);
+  return B200_OK;
+}
+
+template <int BN, int G>
+static int launch_gemm_layout(bool kmajor, const void* A, int64_t lda, const void* B, int64_t ldb,
+                              const GemmParams& p, cudaStream_t stream) {
+  return kmajor ? launch_gemm<BN, G, true>(A, lda, B, ldb, p, stream)
+                : launch_gemm<BN, G, false>(A, lda, B, ldb, p, stream);
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_gemm_set_tuning(int cta_group, int block_n) {
+  if (cta_group < 0 || cta_group > 2) return fail(B200_ERR_INVALID_ARGUMENT, "cta_group must be 0, 1 or 2");
+  if (block_n != 0 && block_n != 64 && block_n != 128 && block_n != 256)
+    return fail(B200_ERR_INVALID_ARGUMENT, "block_n must be 0, 64, 128 or 256");
+  g_force_cta_group = cta_group;
+  g_force_bn = block_n;
+  return B200_OK;
+}
+
+extern "C" int b200_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, int b_layout,
+                              const void* bias, void* C, int64_t ldc, int out_dtype, int M, int N, int K,
+                              int epilogue, void* stream) {
+  B200_REQUIRE(A && B && C, "b200_gemm_bf16: null operand pointer");
+  B200_REQUIRE(M > 0 && N > 0 && K > 0, "b200_gemm_bf16: M, N, K must be positive (got %d, %d, %d)", M, N, K);
+  B200_REQUIRE(K % 8 == 0 && N % 8 == 0, "b200_gemm_bf16: K and N must be multiples of 8 (got K=%d N=%d)", K, N);
+  B200_REQUIRE(b_layout == B200_B_KN || b_layout == B200_B_NK, "b200_gemm_bf16: bad b_layout %d", b_layout);
+  B200_REQUIRE(out_dtype == B200_BF16 || out_dtype == B200_F32, "b200_gemm_bf16: bad out_dtype %d", out_dtype);
+  B200_REQUIRE(epilogue >= B200_EPI_NONE && epilogue <= B200_EPI_GELU_TANH, "b200_gemm_bf16: bad epilogue %d",
+               epilogue);
+  const bool needs_bias =
+      epilogue == B200_EPI_BIAS || epilogue == B200_EPI_BIAS_RELU || epilogue == B200_EPI_BIAS_GELU_TANH;
+  B200_REQUIRE(!needs_bias || bias, "b200_gemm_bf16: epilogue %d needs a bias vector", epilogue);
+  const int64_t min_ldb = b_layout == B200_B_KN ? N : K;
+  B200_REQUIRE(lda >= K && ldb >= min_ldb && ldc >= N, "b200_gemm_bf16: leading dimension smaller than row");
+  B200_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && ldc % 8 == 0, "b200_gemm_bf16: lda/ldb/ldc must be multiples of 8");
+  B200_REQUIRE((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B) | reinterpret_cast<uintptr_t>(C) |
+                reinterpret_cast<uintptr_t>(bias)) % 16 == 0,
+               "b200_gemm_bf16: operands must be 16-byte aligned");
+
+  GemmParams p = {};
+  p.C = C;
+  p.bias = needs_bias ? reinterpret_cast<const __nv_bfloat16*>(bias) : nullptr;
+  p.M = M;
+  p.N = N;
+  p.K = K;
+  p.ldc = ldc;
+  p.epilogue = epilogue;
+  p.out_f32 = out_dtype == B200_F32;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const bool kmajor = b_layout == B200_B_NK;
+
+  // Tile choice: the largest tile that still gives every SM work; CTA pairs once the
+  // problem has at least one 256 x BN tile per pair.
+  const int sms = num_sms();
+  int bn = 256;
+  auto tiles_for = [&](int bm, int bnn) { return ((M + bm - 1) / bm) * ((N + bnn - 1) / bnn); };
+  if (N <= 64 || tiles_for(128, 128) < sms / 2) bn = 64;
+  else if (N <= 128 || tiles_for(128, 256) < sms) bn = 128;
+  int g = (bn >= 128 && tiles_for(256, bn) >= sms / 2) ? 2 : 1;
+  if (g_force_bn) bn = g_force_bn;
+  if (g_force_cta_group) g = g_force_cta_group;
+  if (g == 2 && bn == 64) g = 1;   // a CTA would load 32 B columns: not a whole swizzle chunk
+
+  if (g == 2) {
+    if (bn == 256) return launch_gemm_layout<256, 2>(kmajor, A, lda, B, ldb, p, st);
+    return launch_gemm_layout<128, 2>(kmajor, A, lda, B, ldb, p, st);
+  }
+  if (bn == 256) return launch_gemm_layout<256, 1>(kmajor, A, lda, B, ldb, p, st);
+  if (bn == 128) return launch_gemm_layout<128, 1>(kmajor, A, lda, B, ldb, p, st);
+  return launch_gemm_layout<64, 1>(kmajor, A, lda, B, ldb, p, st);
+}

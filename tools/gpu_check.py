@@ -1,0 +1,140 @@
+"""Bring-up checks run on the GPU box (not part of the test suite): each invocation tests one
+kernel configuration against a torch fp32 computation ON THE GPU and prints error statistics
+and timings.  Run each configuration in its own process (a device trap poisons the context).
+
+  python tools/gpu_check.py gemm --g 1 --layout kn
+  python tools/gpu_check.py gemm_time
+  python tools/gpu_check.py f32
+"""
+import argparse
+import importlib.util
+import os
+import sys
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+spec = importlib.util.spec_from_file_location("capi", os.path.join(ROOT, "learning-jax-sharding_b200", "capi.py"))
+capi = importlib.util.module_from_spec(spec)
+spec.loader.exec_module(capi)
+
+
+def ref_epilogue(acc, bias, epi):
+    v = acc.to(torch.bfloat16).float()
+    if epi in (capi.EPI_BIAS, capi.EPI_BIAS_RELU, capi.EPI_BIAS_GELU_TANH):
+        v = (v + bias.float()).to(torch.bfloat16).float()
+    if epi in (capi.EPI_BIAS_RELU, capi.EPI_RELU):
+        v = torch.relu(v)
+    if epi in (capi.EPI_BIAS_GELU_TANH, capi.EPI_GELU_TANH):
+        v = torch.nn.functional.gelu(v, approximate="tanh")
+    return v
+
+
+def check_gemm(M, N, K, layout, epi=capi.EPI_NONE, out_dtype=torch.bfloat16, seed=0):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    a = torch.randn(M, K, device="cuda", generator=g).to(torch.bfloat16)
+    if layout == "kn":
+        b = (torch.randn(K, N, device="cuda", generator=g) / K ** 0.5).to(torch.bfloat16)
+        ref = a.float() @ b.float()
+    else:
+        b = (torch.randn(N, K, device="cuda", generator=g) / K ** 0.5).to(torch.bfloat16)
+        ref = a.float() @ b.float().t()
+    bias = (torch.randn(N, device="cuda", generator=g) * 0.5).to(torch.bfloat16)
+    out = capi.gemm_bf16(a, b, b_layout=capi.B_KN if layout == "kn" else capi.B_NK, bias=bias, epilogue=epi,
+                         out_dtype=out_dtype)
+    torch.cuda.synchronize()
+    if out_dtype == torch.float32 and epi == capi.EPI_NONE:
+        want = ref
+    else:
+        want = ref_epilogue(ref, bias, epi)
+    got = out.float()
+    err = (got - want).abs()
+    denom = want.abs().clamp_min(1e-2)
+    rel = (err / denom).max().item()
+    bad = (err > 2e-2 * want.abs() + 2e-2).sum().item()
+    print(f"  gemm M={M} N={N} K={K} layout={layout} epi={epi} out={str(out_dtype)[6:]}: "
+          f"max_abs={err.max().item():.3e} max_rel={rel:.3e} bad={bad}/{got.numel()} "
+          f"{'OK' if bad == 0 else 'FAIL'}", flush=True)
+    if bad:
+        idx = (err > 2e-2 * want.abs() + 2e-2).nonzero()[:8]
+        for i, j in idx.tolist():
+            print(f"    [{i},{j}] got={got[i, j].item():.5f} want={want[i, j].item():.5f}")
+        # error structure: which rows / cols are wrong
+        rows = (err > 2e-2 * want.abs() + 2e-2).any(dim=1).nonzero().flatten()
+        cols = (err > 2e-2 * want.abs() + 2e-2).any(dim=0).nonzero().flatten()
+        print(f"    bad rows: n={rows.numel()} first={rows[:6].tolist()} last={rows[-3:].tolist()}; "
+              f"bad cols: n={cols.numel()} first={cols[:6].tolist()} last={cols[-3:].tolist()}")
+    return bad == 0
+
+
+def time_fn(fn, iters=20, warmup=3):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    for _ in range(iters):
+        fn()
+    e.record()
+    torch.cuda.synchronize()
+    return s.elapsed_time(e) / iters
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("what")
+    ap.add_argument("--g", type=int, default=0)
+    ap.add_argument("--bn", type=int, default=0)
+    ap.add_argument("--layout", default="kn")
+    args = ap.parse_args()
+    print(f"== {args.what} g={args.g} bn={args.bn} layout={args.layout} on {torch.cuda.get_device_name(0)}",
+          flush=True)
+    capi.load()
+    ok = True
+    if args.what == "gemm":
+        capi.set_gemm_tuning(args.g, args.bn)
+        shapes = [(128, 256, 64), (256, 256, 128), (256, 512, 256), (512, 640, 512), (2048, 512, 640),
+                  (1000, 264, 136), (4096, 4096, 1024)]
+        for (M, N, K) in shapes:
+            ok &= check_gemm(M, N, K, args.layout)
+        ok &= check_gemm(512, 768, 256, args.layout, epi=capi.EPI_BIAS)
+        ok &= check_gemm(512, 768, 256, args.layout, epi=capi.EPI_BIAS_RELU)
+        ok &= check_gemm(512, 768, 256, args.layout, epi=capi.EPI_BIAS_GELU_TANH)
+        ok &= check_gemm(512, 768, 256, args.layout, epi=capi.EPI_NONE, out_dtype=torch.float32)
+    elif args.what == "gemm_time":
+        for (g, bn) in [(1, 256), (2, 256), (1, 128), (2, 128)]:
+            capi.set_gemm_tuning(g, bn)
+            for layout in ("kn", "nk"):
+                for (M, N, K) in [(8192, 8192, 8192), (16384, 16384, 4096), (16384, 4096, 16384)]:
+                    a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
+                    b = torch.randn((K, N) if layout == "kn" else (N, K), device="cuda").to(torch.bfloat16)
+                    out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+                    lay = capi.B_KN if layout == "kn" else capi.B_NK
+                    ms = time_fn(lambda: capi.gemm_bf16(a, b, b_layout=lay, out=out))
+                    print(f"  g={g} bn={bn} {layout} M={M} N={N} K={K}: {ms:.3f} ms "
+                          f"{2 * M * N * K / ms / 1e9:.1f} TFLOP/s", flush=True)
+        # cuBLAS comparator
+        for (M, N, K) in [(8192, 8192, 8192), (16384, 16384, 4096), (16384, 4096, 16384)]:
+            a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
+            b = torch.randn(K, N, device="cuda").to(torch.bfloat16)
+            ms = time_fn(lambda: torch.matmul(a, b))
+            print(f"  cublas M={M} N={N} K={K}: {ms:.3f} ms {2 * M * N * K / ms / 1e9:.1f} TFLOP/s", flush=True)
+    elif args.what == "f32":
+        for (Bt, M, N, K) in [(1, 4, 4, 16), (8, 4, 4, 16), (1, 2, 1, 16), (1, 257, 129, 77), (1, 1024, 1024, 1024)]:
+            a = torch.randn(Bt, M, K, device="cuda")
+            b = torch.randn(Bt, K, N, device="cuda")
+            out = capi.gemm_f32(a, b)
+            want = (a.double() @ b.double())
+            err = ((out.double() - want).abs() / want.abs().clamp_min(1e-3)).max().item()
+            good = torch.allclose(out.double(), want, rtol=1e-5, atol=1e-5 * K ** 0.5)
+            print(f"  f32 B={Bt} M={M} N={N} K={K}: max_rel={err:.3e} {'OK' if good else 'FAIL'}", flush=True)
+            ok &= good
+    else:
+        raise SystemExit(f"unknown check {args.what}")
+    print("RESULT", "PASS" if ok else "FAIL", flush=True)
+    sys.exit(0 if ok else 1)
+
+
+if __name__ == "__main__":
+    main()
