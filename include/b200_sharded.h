@@ -76,6 +76,18 @@ int b200_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, int b
                    void* C, int64_t ldc, int out_dtype, int M, int N, int K, int epilogue, void* stream);
 
 /*
+ * b200_gemm_bf16 with a row-blocked view of A: logical row m of A is read from physical row
+ *   (m / a_rows_per_block) * a_block_stride + m % a_rows_per_block
+ * (a_rows_per_block a multiple of 128; 0 = plain).  Lets a tensor-parallel layer take the token
+ * chunk "rows [c*R, (c+1)*R) of every rank's sequence block" as ONE GEMM, so that the
+ * reduce-scatter of that chunk lands in contiguous sequence blocks (the layout
+ * PartitionSpec('data','model') gives x and y in case6_attention.py:161,230).
+ */
+int b200_gemm_bf16_rowblocked(const void* A, int64_t lda, int a_rows_per_block, int a_block_stride, const void* B,
+                              int64_t ldb, int b_layout, const void* bias, void* C, int64_t ldc, int out_dtype, int M,
+                              int N, int K, int epilogue, void* stream);
+
+/*
  * Batched true-fp32 GEMM (FFMA, no TF32): for b in [0,batch):
  *   C_b[M,N] = A_b[M,K] . B_b[K,N], all row-major, element strides lda/ldb/ldc
  *   between rows and strideA/strideB/strideC between batch items.

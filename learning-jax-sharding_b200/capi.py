@@ -28,6 +28,7 @@ EXPORTED_SYMBOLS = (
     "b200_last_error",
     "b200_launch_count",
     "b200_gemm_bf16",
+    "b200_gemm_bf16_rowblocked",
     "b200_gemm_f32",
     "b200_attention_fwd",
     "b200_ffn_fwd",
@@ -60,6 +61,7 @@ def load():
     lib.b200_last_error.restype = ctypes.c_char_p
     lib.b200_launch_count.restype = i64
     lib.b200_gemm_bf16.argtypes = [vp, i64, vp, i64, i32, vp, vp, i64, i32, i32, i32, i32, i32, vp]
+    lib.b200_gemm_bf16_rowblocked.argtypes = [vp, i64, i32, i32, vp, i64, i32, vp, vp, i64, i32, i32, i32, i32, i32, vp]
     lib.b200_gemm_f32.argtypes = [vp, i64, i64, vp, i64, i64, vp, i64, i64, i32, i32, i32, i32, i32, vp]
     lib.b200_attention_fwd.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32] + [i64] * 12 + [f32, i32, vp]
     lib.b200_ffn_fwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp]
@@ -105,16 +107,22 @@ def set_gemm_tuning(cta_group: int = 0, block_n: int = 0):
     _check(load().b200_gemm_set_tuning(cta_group, block_n), "b200_gemm_set_tuning")
 
 
-def gemm_bf16(a, b, *, b_layout=B_KN, bias=None, epilogue=EPI_NONE, out=None, out_dtype=torch.bfloat16):
+def gemm_bf16(a, b, *, b_layout=B_KN, bias=None, epilogue=EPI_NONE, out=None, out_dtype=torch.bfloat16,
+              a_row_blocks=None):
     """out[M,N] = epilogue(a[M,K] @ B + bias). ``b`` is [K,N] (B_KN, a Dense kernel) or [N,K] (B_NK).
 
-    a, b, out may be row-strided views (last dim contiguous)."""
+    a, b, out may be row-strided views (last dim contiguous).  ``a_row_blocks=(M, rows_per_block,
+    block_stride)`` reads M logical rows out of a larger ``a`` through the row-blocked view of
+    b200_gemm_bf16_rowblocked."""
     _require_cuda(a, b, bias, out)
     if a.dtype != torch.bfloat16 or b.dtype != torch.bfloat16:
         raise B200Error("gemm_bf16 takes bf16 operands")
     if a.dim() != 2 or b.dim() != 2 or a.stride(1) != 1 or b.stride(1) != 1:
         raise B200Error("gemm_bf16 takes 2-D operands with a contiguous last dim")
     M, K = a.shape
+    rpb = bstride = 0
+    if a_row_blocks is not None:
+        M, rpb, bstride = a_row_blocks
     if b_layout == B_KN:
         Kb, N = b.shape
     else:
@@ -128,8 +136,8 @@ def gemm_bf16(a, b, *, b_layout=B_KN, bias=None, epilogue=EPI_NONE, out=None, ou
     if bias is not None and (bias.dtype != torch.bfloat16 or bias.numel() != N or not bias.is_contiguous()):
         raise B200Error("gemm_bf16: bias must be a contiguous bf16 vector of length N")
     with torch.cuda.device(a.device):
-        rc = load().b200_gemm_bf16(
-            _ptr(a), a.stride(0), _ptr(b), b.stride(0), b_layout, _ptr(bias), _ptr(out), out.stride(0),
+        rc = load().b200_gemm_bf16_rowblocked(
+            _ptr(a), a.stride(0), rpb, bstride, _ptr(b), b.stride(0), b_layout, _ptr(bias), _ptr(out), out.stride(0),
             F32 if out.dtype == torch.float32 else BF16, M, N, K, epilogue, _stream(a))
     _check(rc, "b200_gemm_bf16")
     return out

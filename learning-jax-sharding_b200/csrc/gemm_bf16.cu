@@ -46,6 +46,9 @@ struct GemmParams {
   int epilogue;
   int out_f32;
   int tiles_m, tiles_n;
+  // optional row-blocked view of A: logical row m lives at physical row
+  // (m / a_rows_per_block) * a_block_stride + m % a_rows_per_block   (0 = plain row-major)
+  int a_rows_per_block, a_block_stride;
 };
 
 __device__ __forceinline__ float gelu_tanh_f(float x) {
@@ -135,7 +138,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     for (int tile = worker; tile < num_tiles; tile += num_workers) {
       int m_blk, n_blk;
       tile_coords(tile, p.tiles_m, p.tiles_n, m_blk, n_blk);
-      const int m0 = (m_blk * G + cta_rank) * kBM;
+      int m0 = (m_blk * G + cta_rank) * kBM;
+      if (p.a_rows_per_block > 0) m0 = (m0 / p.a_rows_per_block) * p.a_block_stride + m0 % p.a_rows_per_block;
       const int n0 = n_blk * BN + cta_rank * Cfg::kBNcta;
       for (int kb = 0; kb < num_kb; ++kb) {
         mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -321,7 +325,11 @@ static int launch_gemm(const void* A, int64_t lda, const void* B, int64_t ldb, c
   p.tiles_n = (p.N + BN - 1) / BN;
   CUtensorMap tmA, tmB;
   {
-    uint64_t dims[2] = {static_cast<uint64_t>(p.K), static_cast<uint64_t>(p.M)};
+    uint64_t a_rows = static_cast<uint64_t>(p.M);
+    if (p.a_rows_per_block > 0)
+      a_rows = static_cast<uint64_t>((p.M + p.a_rows_per_block - 1) / p.a_rows_per_block - 1) * p.a_block_stride +
+               p.a_rows_per_block;
+    uint64_t dims[2] = {static_cast<uint64_t>(p.K), a_rows};
     uint64_t strides[2] = {0, static_cast<uint64_t>(lda) * 2};
     uint32_t box[2] = {kBK, kBM};
     int rc = make_tensor_map(&tmA, A, 2, 2, dims, strides, box, 3);
@@ -386,7 +394,18 @@ extern "C" int b200_gemm_set_tuning(int cta_group, int block_n) {
 extern "C" int b200_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, int b_layout,
                               const void* bias, void* C, int64_t ldc, int out_dtype, int M, int N, int K,
                               int epilogue, void* stream) {
+  return b200_gemm_bf16_rowblocked(A, lda, 0, 0, B, ldb, b_layout, bias, C, ldc, out_dtype, M, N, K, epilogue,
+                                   stream);
+}
+
+extern "C" int b200_gemm_bf16_rowblocked(const void* A, int64_t lda, int a_rows_per_block, int a_block_stride,
+                                         const void* B, int64_t ldb, int b_layout, const void* bias, void* C,
+                                         int64_t ldc, int out_dtype, int M, int N, int K, int epilogue,
+                                         void* stream) {
   B200_REQUIRE(A && B && C, "b200_gemm_bf16: null operand pointer");
+  B200_REQUIRE(a_rows_per_block >= 0 && a_block_stride >= 0, "b200_gemm_bf16: negative row-block parameters");
+  B200_REQUIRE(a_rows_per_block == 0 || (a_rows_per_block % 128 == 0 && a_block_stride >= a_rows_per_block),
+               "b200_gemm_bf16: a_rows_per_block must be a multiple of 128 and <= a_block_stride");
   B200_REQUIRE(M > 0 && N > 0 && K > 0, "b200_gemm_bf16: M, N, K must be positive (got %d, %d, %d)", M, N, K);
   B200_REQUIRE(K % 8 == 0 && N % 8 == 0, "b200_gemm_bf16: K and N must be multiples of 8 (got K=%d N=%d)", K, N);
   B200_REQUIRE(b_layout == B200_B_KN || b_layout == B200_B_NK, "b200_gemm_bf16: bad b_layout %d", b_layout);
@@ -412,6 +431,8 @@ extern "C" int b200_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t
   p.ldc = ldc;
   p.epilogue = epilogue;
   p.out_f32 = out_dtype == B200_F32;
+  p.a_rows_per_block = a_rows_per_block;
+  p.a_block_stride = a_block_stride;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const bool kmajor = b_layout == B200_B_NK;
 

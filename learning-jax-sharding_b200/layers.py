@@ -1,0 +1,320 @@
+"""Resident-weight sharded layers for the throughput path (BASELINE.json configs): one process per
+GPU, weights pre-sharded and resident in HBM (placement is outside the timed region, as in the
+reference's loop, case6_attention.py:234-238), per-shard compute through the C ABI, collectives
+on a side stream overlapped with the GEMMs of the next token chunk.
+
+  TensorParallelFFN   W1 P(None,'model') column-parallel, W2 P('model',None) row-parallel; the
+                      partial y of token chunk c is reduce-scattered (NCCL over NVLink) while the
+                      GEMMs of chunk c+1 run; y comes back sequence-sharded P('model') like x_sharding.
+  FsdpFFN             W1/W2 P('data',None): tokens sharded over 'data', each weight all-gathered
+                      in column chunks that overlap the previous chunk's GEMM.
+"""
+from __future__ import annotations
+
+import json
+import os
+from typing import Optional
+
+import torch
+
+from . import capi
+
+
+def _act_code(act: str, bias: bool) -> int:
+    if act == "gelu_tanh":
+        return capi.EPI_BIAS_GELU_TANH if bias else capi.EPI_GELU_TANH
+    if act == "relu":
+        return capi.EPI_BIAS_RELU if bias else capi.EPI_RELU
+    raise ValueError(f"unknown activation {act!r}")
+
+
+class TensorParallelFFN:
+    """y = act(x.W1 + b1).W2 + b2 with d_ff sharded over the `world` ranks of `group`.
+
+    x: [T, d_model] bf16, replicated over the group.  Returns this rank's sequence block
+    y[rank*T/world : (rank+1)*T/world] (reduce-scatter), bf16.  world == 1 is the plain two-GEMM
+    layer.  The partial sums cross NVLink in bf16 (NCCL accumulates each hop in f32): half the
+    bytes of f32 partials, inside the bf16 parity bar."""
+
+    def __init__(self, w1, b1, w2, b2, act: str, T: int, group=None, chunks: int = 4):
+        self.w1, self.b1, self.w2, self.b2 = w1, b1, w2, b2
+        self.act = _act_code(act, b1 is not None)
+        self.d_model, self.F = w1.shape
+        self.T = T
+        self.group = group
+        if group is not None:
+            import torch.distributed as dist
+            self.dist = dist
+            self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        else:
+            self.world, self.rank = 1, 0
+        dev = w1.device
+        self.h = torch.empty((T, self.F), dtype=torch.bfloat16, device=dev)
+        if self.world == 1:
+            self.y = torch.empty((T, self.d_model), dtype=torch.bfloat16, device=dev)
+            self.chunks = 1
+        else:
+            while chunks > 1 and (T % (self.world * chunks) or (T // (self.world * chunks)) % 128):
+                chunks //= 2
+            self.chunks = max(chunks, 1)
+            if T % self.world or (T // self.world // self.chunks) % 128:
+                raise ValueError(f"T={T} must split into {self.world} x {self.chunks} blocks of a multiple of 128 rows")
+            self.ypart = torch.empty((T, self.d_model), dtype=torch.bfloat16, device=dev)
+            self.y = torch.empty((T // self.world, self.d_model), dtype=torch.bfloat16, device=dev)
+            self.comm_stream = torch.cuda.Stream(device=dev)
+            self.chunk_done = [torch.cuda.Event() for _ in range(self.chunks)]
+        self.kernel_events = None
+
+    def forward(self, x: torch.Tensor, record=None) -> torch.Tensor:
+        if self.world == 1:
+            if record is not None:
+                record("start")
+            capi.gemm_bf16(x, self.w1, bias=self.b1, epilogue=self.act, out=self.h)
+            if record is not None:
+                record("gemm1")
+            capi.gemm_bf16(self.h, self.w2, bias=self.b2, epilogue=capi.EPI_BIAS if self.b2 is not None else capi.EPI_NONE,
+                           out=self.y)
+            if record is not None:
+                record("gemm2")
+            return self.y
+        W, C, T = self.world, self.chunks, self.T
+        rows_blk = T // W // C                  # rows of one (rank block, chunk) cell
+        rows_chunk = rows_blk * W               # logical rows of one chunk GEMM
+        main = torch.cuda.current_stream(x.device)
+        self.comm_stream.wait_stream(main)      # previous step's consumers of y / ypart are done
+        for c in range(C):
+            hc = self.h[c * rows_chunk:(c + 1) * rows_chunk]
+            yc = self.ypart[c * rows_chunk:(c + 1) * rows_chunk]
+            # chunk c = rows [c*rows_blk, (c+1)*rows_blk) of EVERY rank's sequence block of x
+            xa = x[c * rows_blk:]
+            if record is not None:
+                record("start")
+            capi.gemm_bf16(xa, self.w1, bias=self.b1, epilogue=self.act, out=hc,
+                           a_row_blocks=(rows_chunk, rows_blk, T // W))
+            if record is not None:
+                record("gemm1")
+            # b2 enters the sum exactly once: on rank 0's partial
+            b2 = self.b2 if (self.rank == 0 and self.b2 is not None) else None
+            capi.gemm_bf16(hc, self.w2, bias=b2, epilogue=capi.EPI_BIAS if b2 is not None else capi.EPI_NONE, out=yc)
+            if record is not None:
+                record("gemm2")
+            self.chunk_done[c].record(main)
+            with torch.cuda.stream(self.comm_stream):
+                self.comm_stream.wait_event(self.chunk_done[c])
+                self.dist.reduce_scatter_tensor(self.y[c * rows_blk:(c + 1) * rows_blk], yc, group=self.group)
+        main.wait_stream(self.comm_stream)
+        return self.y
+
+
+class FsdpFFN:
+    """FSDP layout (BASELINE.json case3 config): tokens sharded over 'data' (this rank holds
+    x[T/world rows]); W1 [d_model, d_ff] and W2 [d_ff, d_model] are dim0-sharded over 'data'.
+    Each weight is all-gathered in `chunks` column chunks on a side stream; the GEMM on column
+    chunk j runs while chunk j+1 (and then W2's chunks) are in flight."""
+
+    def __init__(self, w1_shard, b1, w2_shard, b2, act: str, T_local: int, group, chunks: int = 4):
+        import torch.distributed as dist
+        self.dist, self.group = dist, group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.w1s, self.b1, self.w2s, self.b2 = w1_shard, b1, w2_shard, b2
+        self.act = _act_code(act, b1 is not None)
+        self.d_model = w1_shard.shape[0] * self.world
+        self.F = w1_shard.shape[1]
+        self.T = T_local
+        self.chunks = chunks
+        dev = w1_shard.device
+        # gathered weights, chunk-major: [chunk][K rows][cols/chunks]
+        self.w1g = torch.empty((chunks, self.d_model, self.F // chunks), dtype=torch.bfloat16, device=dev)
+        self.w2g = torch.empty((chunks, self.F, self.d_model // chunks), dtype=torch.bfloat16, device=dev)
+        # column-chunked views of the local shards must be contiguous for NCCL: keep a chunk-major copy
+        self.w1s_c = w1_shard.reshape(w1_shard.shape[0], chunks, -1).permute(1, 0, 2).contiguous()
+        self.w2s_c = w2_shard.reshape(w2_shard.shape[0], chunks, -1).permute(1, 0, 2).contiguous()
+        self.h = torch.empty((T_local, self.F), dtype=torch.bfloat16, device=dev)
+        self.y = torch.empty((T_local, self.d_model), dtype=torch.bfloat16, device=dev)
+        self.comm_stream = torch.cuda.Stream(device=dev)
+        self.ready = [torch.cuda.Event() for _ in range(2 * chunks)]
+
+    def forward(self, x: torch.Tensor, record=None) -> torch.Tensor:
+        C = self.chunks
+        main = torch.cuda.current_stream(x.device)
+        self.comm_stream.wait_stream(main)
+        with torch.cuda.stream(self.comm_stream):
+            for j in range(C):
+                self.dist.all_gather_into_tensor(self.w1g[j], self.w1s_c[j], group=self.group)
+                self.ready[j].record(self.comm_stream)
+            for j in range(C):
+                self.dist.all_gather_into_tensor(self.w2g[j], self.w2s_c[j], group=self.group)
+                self.ready[C + j].record(self.comm_stream)
+        fc, dc = self.F // C, self.d_model // C
+        for j in range(C):
+            main.wait_event(self.ready[j])
+            if record is not None:
+                record("start")
+            b = self.b1[j * fc:(j + 1) * fc] if self.b1 is not None else None
+            capi.gemm_bf16(x, self.w1g[j], bias=b, epilogue=self.act, out=self.h[:, j * fc:(j + 1) * fc])
+            if record is not None:
+                record("gemm1")
+        for j in range(C):
+            main.wait_event(self.ready[C + j])
+            if record is not None:
+                record("start")
+            b = self.b2[j * dc:(j + 1) * dc] if self.b2 is not None else None
+            capi.gemm_bf16(self.h, self.w2g[j], bias=b, epilogue=capi.EPI_BIAS if b is not None else capi.EPI_NONE,
+                           out=self.y[:, j * dc:(j + 1) * dc])
+            if record is not None:
+                record("gemm2")
+        return self.y
+
+
+# ------------------------------------------------------------------------ bench harness glue
+def _synthetic(shape, seed, kind, fan_in=None, device="cuda"):
+    """Seeded synthetic tensors of SURVEY.md §8d, generated on the host like the oracle's."""
+    g = torch.Generator().manual_seed(seed)
+    t = torch.randn(shape, generator=g, dtype=torch.float32)
+    if kind == "weight":
+        t = t / (fan_in if fan_in is not None else shape[0]) ** 0.5
+    elif kind == "bias":
+        t = t * 0.02
+    return t
+
+
+class FFNBench:
+    """Builds the case4 (TP) / case3 (FSDP) FFN workload for this rank and exposes the two step
+    functions bench.py times: `step_resident` (inputs in HBM) and `step_e2e` (x from pinned host
+    memory, y back to pinned host memory, in token chunks so copies overlap the GEMMs)."""
+
+    def __init__(self, cfg, act, rank, world, dev, chunks=4):
+        self.cfg, self.rank, self.world, self.dev = cfg, rank, world, dev
+        T, d, f = cfg["batch"] * cfg["seq"], cfg["d_model"], cfg["d_ff"]
+        self.T, self.d, self.f = T, d, f
+        self.mode = cfg.get("parallelism", "tp") if world > 1 else "single"
+        group = None
+        if world > 1:
+            import torch.distributed as dist
+            group = dist.group.WORLD
+        x = _synthetic((T, d), 0, "activation").to(torch.bfloat16)
+        w1 = _synthetic((d, f), 1, "weight").to(torch.bfloat16)
+        b1 = _synthetic((f,), 2, "bias").to(torch.bfloat16)
+        w2 = _synthetic((f, d), 3, "weight").to(torch.bfloat16)
+        b2 = _synthetic((d,), 4, "bias").to(torch.bfloat16)
+        if self.mode == "fsdp":
+            tl, kl1, kl2 = T // world, d // world, f // world
+            self.x_host = x[rank * tl:(rank + 1) * tl].contiguous().pin_memory()
+            self.layer = FsdpFFN(w1[rank * kl1:(rank + 1) * kl1].to(dev), b1.to(dev), w2[rank * kl2:(rank + 1) * kl2].to(dev),
+                                 b2.to(dev), act, tl, group, chunks=chunks)
+            self.T_in, self.T_out = tl, tl
+        else:
+            fl = f // world
+            self.x_host = x.pin_memory()
+            self.layer = TensorParallelFFN(w1[:, rank * fl:(rank + 1) * fl].contiguous().to(dev),
+                                           b1[rank * fl:(rank + 1) * fl].contiguous().to(dev),
+                                           w2[rank * fl:(rank + 1) * fl].contiguous().to(dev), b2.to(dev), act, T, group,
+                                           chunks=chunks)
+            self.T_in, self.T_out = T, T // world
+        self.x = self.x_host.to(dev)
+        self.y_host = torch.empty((self.T_out, d), dtype=torch.bfloat16).pin_memory()
+        self.x_stage = torch.empty_like(self.x)
+        self.copy_in = torch.cuda.Stream(device=dev)
+        self.copy_out = torch.cuda.Stream(device=dev)
+        self._events = []
+        self._pending = None
+
+    def parallelism_name(self):
+        if self.mode == "single":
+            return "1 GPU"
+        return f"{'tp' if self.mode == 'tp' else 'fsdp'}{self.world} (mesh {'1x%d' % self.world if self.mode == 'tp' else '%dx1' % self.world})"
+
+    # --- kernel-resident step
+    def reset_kernel_events(self):
+        self._events = []
+
+    def _record(self, tag):
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record()
+        self._events.append((tag, ev))
+
+    def step_resident(self, record_kernels=False):
+        return self.layer.forward(self.x, record=self._record if record_kernels else None)
+
+    def mean_kernel_ms(self):
+        """Mean device time of one GEMM launch, from events recorded around every launch of the timed region."""
+        total, n = 0.0, 0
+        prev = None
+        for tag, ev in self._events:
+            if tag != "start" and prev is not None:
+                total += prev.elapsed_time(ev)
+                n += 1
+            prev = ev
+        return total / max(n, 1)
+
+    # --- end-to-end step: host x -> device -> FFN -> host y
+    def step_e2e(self):
+        main = torch.cuda.current_stream(self.dev)
+        self.copy_in.wait_stream(main)
+        with torch.cuda.stream(self.copy_in):
+            self.x_stage.copy_(self.x_host, non_blocking=True)
+        main.wait_stream(self.copy_in)
+        y = self.layer.forward(self.x_stage)
+        self.copy_out.wait_stream(main)
+        with torch.cuda.stream(self.copy_out):
+            self.y_host.copy_(y, non_blocking=True)
+        main.wait_stream(self.copy_out)
+        return self.y_host
+
+    def e2e_bytes(self):
+        return self.x_host.numel() * 2, self.y_host.numel() * 2
+
+    def ncu_traffic_bytes(self):
+        """dram read+write bytes per GEMM launch from the committed ncu --set full capture, if any."""
+        path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles", "ncu_traffic.json")
+        if os.path.exists(path):
+            try:
+                with open(path) as f:
+                    return json.load(f).get("gemm_bf16_kernel_bytes_per_launch")
+            except (OSError, ValueError):
+                return None
+        return None
+
+
+def bench_attention(args, cfg, rank, world, dev, metric, unit, peaks, sampler, attn_flops):
+    """Measurement aid for the attention configs (case5 / case6 of BASELINE.json): attention core and
+    core + projections on one GPU; head-sharded over `world` GPUs when launched under torchrun."""
+    B, S, H, D, M = cfg["batch"], cfg["seq"], cfg["heads"], cfg["dim_head"], cfg["d_model"]
+    causal = cfg["causal"]
+    if H % world:
+        raise SystemExit(f"{H} heads do not split over {world} GPUs")
+    hl = H // world
+    q, k, v = (torch.randn((B, S, hl, D), device=dev, dtype=torch.float32).to(torch.bfloat16) for _ in range(3))
+    o = torch.empty_like(q)
+    for _ in range(args.warmup):
+        capi.attention_fwd(q, k, v, causal=causal, out=o)
+    torch.cuda.synchronize(dev)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    l0 = capi.launch_count()
+    e0.record()
+    for _ in range(args.steps):
+        capi.attention_fwd(q, k, v, causal=causal, out=o)
+    e1.record()
+    torch.cuda.synchronize(dev)
+    clocks = sampler.stop()
+    ms = e0.elapsed_time(e1) / args.steps
+    if world > 1:
+        import torch.distributed as dist
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    core, proj = attn_flops(cfg)
+    if rank == 0:
+        val = core / (ms * 1e-3) / 1e12
+        print(json.dumps({
+            "metric": metric, "value": val, "unit": unit, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16",
+            "data": "synthetic",
+            "config": {"workload": args.workload + " (attention core only)", "batch": B, "seq_len": S, "heads": H,
+                       "dim_head": D, "causal": causal, "parallelism": f"heads/{world}", "flops_per_step": core},
+            "clocks": clocks, "gpu_launches": int(capi.launch_count() - l0),
+            "roofline": {"bound": "tensor", "kernel": "attention_fwd_kernel", "achieved": val / world,
+                         "peak": peaks["bf16_burst"], "unit": unit, "frac": val / world / peaks["bf16_burst"],
+                         "peak_source": peaks["source"], "traffic": None},
+            "cpu_baseline": None, "e2e": None}), flush=True)

@@ -1,0 +1,338 @@
+"""Sharded layers behind the Flax surface the reference scripts use: logical-axis rules,
+``Dense``, softmax attention and the feed-forward block.
+
+Reference call sites:
+  nn.Dense(.., dtype=bf16)                         case6_attention.py:61-90,96-99,139; case5_attention_dense.py:59-67
+  nn.with_logical_partitioning / with_logical_constraint / axis_rules / logical_to_mesh_sharding
+                                                   case6_attention.py:56-59,85-88,105-107,114-116,137,141,183-191
+  attention core (einsum, softmax, einsum)         case6_attention.py:121-135
+  FFN  y = act(x.Win).Wout (comment only)          case6_attention.py:36-40
+
+Every layer picks its collectives from the operands' PartitionSpecs (what GSPMD does for the
+reference) and runs the per-shard compute through the C ABI (``runtime.local_compute()``).
+"""
+from __future__ import annotations
+
+import contextlib
+import math
+import threading
+from typing import Dict, Optional, Sequence, Tuple
+
+import torch
+
+from . import runtime as _rt
+from .array import ShardedArray, device_put, reshard
+from .sharding import Mesh, NamedSharding, PartitionSpec, current_mesh
+
+# ------------------------------------------------------------------ logical axis rules
+_rules = threading.local()
+
+
+@contextlib.contextmanager
+def axis_rules(rules: Sequence[Tuple[str, Optional[str]]]):
+    """``with nn_partitioning.axis_rules(rules):`` (case6_attention.py:234)."""
+    stack = getattr(_rules, "stack", None)
+    if stack is None:
+        stack = _rules.stack = []
+    stack.append(tuple(rules))
+    try:
+        yield
+    finally:
+        stack.pop()
+
+
+def current_rules():
+    stack = getattr(_rules, "stack", None)
+    if not stack:
+        raise RuntimeError("no logical axis rules: use `with axis_rules(rules):`")
+    return stack[-1]
+
+
+def logical_to_mesh_axes(names: Sequence[Optional[str]], rules=None) -> PartitionSpec:
+    """Flax ``logical_to_mesh_axes``: rules are tried in order, a mesh axis is used at most once
+    per array, a logical name with no applicable rule is left unsharded, ``None`` is replicated."""
+    rules = current_rules() if rules is None else rules
+    used = set()
+    out = []
+    for name in names:
+        axis = None
+        if name is not None:
+            for lname, maxis in rules:
+                if lname == name and maxis is not None and maxis not in used:
+                    axis = maxis
+                    break
+        if axis is not None:
+            used.add(axis)
+        out.append(axis)
+    return PartitionSpec(*out)
+
+
+def logical_to_mesh_sharding(names, mesh: Mesh, rules) -> NamedSharding:
+    return NamedSharding(mesh, logical_to_mesh_axes(names, rules))
+
+
+def with_logical_constraint(x: ShardedArray, names: Sequence[Optional[str]]) -> ShardedArray:
+    """Reshard ``x`` to the mesh sharding its logical names translate to (the resharding points of
+    case6_attention.py:105-107,114-116,137,141)."""
+    mesh = current_mesh()
+    if mesh is None:
+        raise RuntimeError("with_logical_constraint needs an active mesh (`with mesh:`)")
+    return reshard(x, NamedSharding(mesh, logical_to_mesh_axes(names)))
+
+
+# ----------------------------------------------------------------------------- helpers
+def _axes(x: ShardedArray):
+    if not isinstance(x.sharding, NamedSharding):
+        raise TypeError("sharded layers take NamedSharding operands")
+    return x.sharding.dim_axes(x.ndim)
+
+
+def _spec(axes_per_dim) -> PartitionSpec:
+    return PartitionSpec(*[None if not a else (a[0] if len(a) == 1 else tuple(a)) for a in axes_per_dim])
+
+
+def _to_bf16(t: torch.Tensor) -> torch.Tensor:
+    if t.dtype == torch.bfloat16:
+        return t
+    return _rt.local_compute().cast_f32_to_bf16(t)
+
+
+# ------------------------------------------------------------------------------- Dense
+def dense(x: ShardedArray, kernel: ShardedArray, bias: Optional[ShardedArray] = None, *, epilogue: str = "none",
+          scatter_dim: Optional[int] = None) -> ShardedArray:
+    """``y = bf16(x) @ bf16(kernel) (+ bf16(bias))`` on sharded operands.  ``epilogue`` in
+    {"none", "relu", "gelu_tanh"} is fused into the GEMM.  Plans (m = a mesh axis):
+
+      kernel dim0 over m, x features unsharded   -> all-gather kernel over m   (FSDP; case5, case6 q/k/v)
+      x features and kernel dim0 both over m     -> local partial products (f32) + all-reduce over m
+                                                    (row-parallel; FFN W2, head-sharded out-proj);
+                                                    with ``scatter_dim`` a reduce-scatter that leaves
+                                                    that row dim of y sharded over m instead
+      kernel dim1 over m                         -> column-parallel, y features sharded over m
+                                                    (FFN W1; case6 to_out_0), no communication
+    """
+    rt = _rt.get_runtime()
+    comp = _rt.local_compute()
+    mesh = x.sharding.mesh
+    xa = _axes(x)
+    kw, nw = _axes(kernel)
+    rows, kx = xa[:-1], xa[-1]
+    row_axes = {a for r in rows for a in r}
+    # y's feature dim cannot reuse a mesh axis the rows of x already use: gather the kernel there
+    nw_eff = tuple(a for a in nw if a not in row_axes)
+    if nw_eff != nw:
+        kernel = reshard(kernel, NamedSharding(mesh, _spec([kw, nw_eff])))
+    if kx and kw and kx != kw:
+        x = reshard(x, NamedSharding(mesh, _spec(list(rows) + [()])))
+        kx = ()
+    if kw and not kx:
+        kernel = reshard(kernel, NamedSharding(mesh, _spec([(), nw_eff])))      # FSDP all-gather
+        kw = ()
+    if kx and not kw:
+        kernel = reshard(kernel, NamedSharding(mesh, _spec([kx, nw_eff])))      # local row slicing
+        kw = kx
+    if bias is not None and nw_eff:
+        bias = reshard(bias, NamedSharding(mesh, _spec([nw_eff])))
+    elif bias is not None and not bias.sharding.is_fully_replicated(bias.shape):
+        bias = reshard(bias, NamedSharding(mesh, PartitionSpec()))
+
+    reduce_axes = kx                      # == kw here; () when the contraction is local
+    epi_code = {"none": 0, "relu": 1, "gelu_tanh": 2}[epilogue]
+    from . import capi as C
+    out_local = {}
+    for d in rt.local_device_ids:
+        xs = x.shard(d)
+        lead = xs.shape[:-1]
+        x2 = _to_bf16(xs.reshape(-1, xs.shape[-1]))
+        w = _to_bf16(kernel.shard(d))
+        b = _to_bf16(bias.shard(d)) if bias is not None else None
+        if reduce_axes:
+            y2 = comp.gemm_bf16(x2, w, out_dtype=torch.float32)          # raw f32 partials
+        else:
+            if b is not None:
+                epi = (C.EPI_BIAS, C.EPI_BIAS_RELU, C.EPI_BIAS_GELU_TANH)[epi_code]
+            else:
+                epi = (C.EPI_NONE, C.EPI_RELU, C.EPI_GELU_TANH)[epi_code]
+            y2 = comp.gemm_bf16(x2, w, bias=b, epilogue=epi)
+        out_local[d] = y2.reshape(*lead, y2.shape[-1])
+
+    out_rows = [tuple(r) for r in rows]
+    if reduce_axes:
+        if epi_code != 0:
+            raise NotImplementedError("an activation cannot be fused into a row-parallel partial product")
+        groups = mesh.axis_groups(reduce_axes)
+        if scatter_dim is not None:
+            out_local = rt.reduce_scatter(out_local, groups, dim=scatter_dim)
+            out_rows[scatter_dim] = out_rows[scatter_dim] + tuple(reduce_axes)
+        else:
+            out_local = rt.all_reduce(out_local, groups)
+        for d in list(out_local):
+            t = out_local[d]
+            b = _to_bf16(bias.shard(d)) if bias is not None else None
+            y2 = comp.sum_partials_to_bf16(t.reshape(1, -1, t.shape[-1]).contiguous(), bias=b)
+            out_local[d] = y2.reshape(t.shape)
+    out_shape = x.shape[:-1] + (kernel.shape[1],)
+    return ShardedArray(out_shape, torch.bfloat16, NamedSharding(mesh, _spec(out_rows + [nw_eff])), out_local)
+
+
+# ------------------------------------------------------------------------------ attention
+def split_heads(x: ShardedArray, heads: int) -> ShardedArray:
+    """(b, S, N*D) -> (b, S, N, D); a view on every shard (case6_attention.py:109-112).  A mesh axis on
+    the feature dim moves to the heads dim."""
+    xa = _axes(x)
+    d_head = x.shape[-1] // heads
+    nparts = 1
+    for a in xa[-1]:
+        nparts *= x.sharding.mesh.axis_size(a)
+    if heads % nparts:
+        raise ValueError(f"{heads} heads cannot be split over {nparts} devices")
+    shards = {d: t.reshape(*t.shape[:-1], heads // nparts, d_head) for d, t in x.local_shards.items()}
+    spec = _spec(list(xa[:-1]) + [xa[-1], ()])
+    return ShardedArray(x.shape[:-1] + (heads, d_head), x.dtype, NamedSharding(x.sharding.mesh, spec), shards)
+
+
+def merge_heads(x: ShardedArray) -> ShardedArray:
+    """(b, S, N, D) -> (b, S, N*D) (case6_attention.py:135)."""
+    xa = _axes(x)
+    if xa[-1]:
+        raise ValueError("the head dim (D) must not be sharded")
+    shards = {d: t.reshape(*t.shape[:-2], t.shape[-2] * t.shape[-1]) for d, t in x.local_shards.items()}
+    spec = _spec(list(xa[:-2]) + [xa[-2]])
+    return ShardedArray(x.shape[:-2] + (x.shape[-2] * x.shape[-1],), x.dtype, NamedSharding(x.sharding.mesh, spec),
+                        shards)
+
+
+def dot_product_attention(q: ShardedArray, k: ShardedArray, v: ShardedArray, *, scale: Optional[float] = None,
+                          causal: bool = False) -> ShardedArray:
+    """softmax(scale q k^T) v on (b, S, N, D) arrays (case6_attention.py:121-135).  Batch and head
+    dims may be sharded (no communication: head-sharded attention); a sequence-sharded q keeps its
+    query block while k and v are all-gathered along S (the literal case6 layout)."""
+    rt = _rt.get_runtime()
+    comp = _rt.local_compute()
+    mesh = q.sharding.mesh
+    qa, ka = _axes(q), _axes(k)
+    if ka[1]:
+        full_kv = NamedSharding(mesh, _spec([ka[0], (), ka[2], ka[3]]))
+        k = reshard(k, full_kv)
+        v = reshard(v, full_kv)
+    S = q.shape[1]
+    out = {}
+    for d in rt.local_device_ids:
+        ql, kl, vl = q.shard(d), k.shard(d), v.shard(d)
+        if causal and qa[1]:
+            # a query block of a sequence-sharded q attends to keys up to its own global positions
+            f0, f1 = q.index_of(d)[1].start, q.index_of(d)[1].stop
+            kl, vl = kl[:, :f1], vl[:, :f1]
+        out[d] = comp.attention_fwd(ql, kl, vl, scale=scale, causal=causal)
+    return ShardedArray(q.shape, torch.bfloat16, q.sharding, out)
+
+
+# ------------------------------------------------------------------------------------ FFN
+def ffn(x: ShardedArray, w1: ShardedArray, b1: Optional[ShardedArray], w2: ShardedArray, b2: Optional[ShardedArray], *,
+        act: str = "gelu_tanh", scatter_dim: Optional[int] = None) -> ShardedArray:
+    """y = act(x.W1 + b1).W2 + b2 (case6_attention.py:36-40).  With W1 ``P(None,'model')`` and W2
+    ``P('model',None)`` this is the column-parallel -> activation -> row-parallel block: one
+    all-reduce (or reduce-scatter with ``scatter_dim``) over 'model' at the end.  With W1/W2
+    ``P('data',None)`` the weights are all-gathered first (FSDP)."""
+    h = dense(x, w1, b1, epilogue=act)
+    return dense(h, w2, b2, scatter_dim=scatter_dim)
+
+
+# ------------------------------------------------------------------- modules / parameters
+def _init_normal(shape, fan_in, seed) -> torch.Tensor:
+    g = torch.Generator().manual_seed(seed)
+    return torch.randn(shape, generator=g, dtype=torch.float32) / math.sqrt(fan_in)
+
+
+class FlaxAttention:
+    """The reference's attention module (case6_attention.py:42-143): q/k/v Dense without bias,
+    f32 softmax attention, to_out_0 Dense with bias, dropout(0) = identity.
+
+    ``layout="literal"`` keeps the reference's annotations (activations sequence-sharded through the
+    logical name 'embed', heads replicated, case6_attention.py:105-107,114-116); ``layout="heads"``
+    is the modified annotation set BASELINE.json's case6 config asks for: rule
+    ('heads','model') in place of ('embed','model'), q/k/v constrained to ('batch', None, 'heads'),
+    out-projection row-parallel with a reduce-scatter back to the sequence-sharded output."""
+
+    def __init__(self, query_dim: int, heads: int = 8, dim_head: int = 64, causal: bool = False,
+                 layout: str = "literal"):
+        self.query_dim, self.heads, self.dim_head = query_dim, heads, dim_head
+        self.scale = dim_head ** -0.5                      # case6_attention.py:51
+        self.causal = causal
+        self.layout = layout
+
+    # logical names of the parameters (case6_attention.py:56-59,85-88)
+    param_axes = {"to_q": ("embed", "heads"), "to_k": ("embed", "heads"), "to_v": ("embed", "heads"),
+                  "to_out_0": ("heads", "embed")}
+
+    def init_host(self, seed: int = 1) -> Dict[str, object]:
+        """lecun-normal-like f32 parameters on the host (stand-in for model.init, case6_attention.py:171-178)."""
+        inner = self.heads * self.dim_head
+        return {
+            "to_q": _init_normal((self.query_dim, inner), self.query_dim, seed),
+            "to_k": _init_normal((self.query_dim, inner), self.query_dim, seed + 1),
+            "to_v": _init_normal((self.query_dim, inner), self.query_dim, seed + 2),
+            "to_out_0": (_init_normal((inner, self.query_dim), inner, seed + 3), torch.zeros(self.query_dim)),
+        }
+
+    def shard_params(self, host_params, mesh: Mesh, rules) -> Dict[str, object]:
+        """Place parameters with the sharding their logical axes translate to
+        (nn.logical_to_mesh_sharding, case6_attention.py:189-191)."""
+        out = {}
+        for name, value in host_params.items():
+            sh = logical_to_mesh_sharding(self.param_axes[name], mesh, rules)
+            if name == "to_out_0":
+                kernel, bias = value
+                out[name] = (device_put(kernel, sh), device_put(bias, NamedSharding(mesh, PartitionSpec())))
+            else:
+                out[name] = device_put(value, sh)
+        return out
+
+    def __call__(self, params, hidden_states: ShardedArray) -> ShardedArray:
+        x = hidden_states
+        if self.layout == "heads":
+            x = with_logical_constraint(x, ("batch", None, None))          # gather the sequence on entry
+        q = dense(x, params["to_q"])                                        # :96
+        k = dense(x, params["to_k"])                                        # :98
+        v = dense(x, params["to_v"])                                        # :99
+        act_names = ("batch", "embed", None) if self.layout == "literal" else ("batch", None, "heads")
+        q, k, v = (with_logical_constraint(t, act_names) for t in (q, k, v))   # :105-107
+        q, k, v = (split_heads(t, self.heads) for t in (q, k, v))               # :109-112
+        names4 = ("batch", "embed", None, None) if self.layout == "literal" else ("batch", None, "heads", None)
+        q, k, v = (with_logical_constraint(t, names4) for t in (q, k, v))       # :114-116
+        o = dot_product_attention(q, k, v, scale=self.scale, causal=self.causal)   # :121-133
+        o = merge_heads(o)                                                  # :135
+        o = with_logical_constraint(o, ("batch", "kv", "heads"))            # :137
+        w_o, b_o = params["to_out_0"]
+        if self.layout == "heads":
+            y = dense(o, w_o, b_o, scatter_dim=1)      # row-parallel + reduce-scatter to S-sharded
+            return y
+        y = dense(o, w_o, b_o)                                              # :139
+        return with_logical_constraint(y, ("batch", "embed"))               # :141 (dropout(0) = identity, :143)
+
+
+# ------------------------------------------------------------------------------------ jit
+def jit(fn, in_shardings=None, out_shardings=None):
+    """``jax.jit(fn, in_shardings=.., out_shardings=..)`` as the scripts use it
+    (case6_attention.py:229-232): arguments that are ShardedArrays are moved to ``in_shardings``
+    if they are not there already, results to ``out_shardings``.  There is no tracing compiler --
+    the layers are already kernels; this only pins the boundary shardings."""
+
+    def _apply(tree, shardings):
+        if shardings is None:
+            return tree
+        if isinstance(tree, ShardedArray):
+            return reshard(tree, shardings)
+        if isinstance(tree, dict):
+            return {k: _apply(v, shardings[k] if isinstance(shardings, dict) else shardings) for k, v in tree.items()}
+        if isinstance(tree, (tuple, list)):
+            sh = shardings if isinstance(shardings, (tuple, list)) else [shardings] * len(tree)
+            return type(tree)(_apply(v, s) for v, s in zip(tree, sh))
+        return tree
+
+    def wrapped(*args):
+        if in_shardings is not None:
+            args = tuple(_apply(a, s) for a, s in zip(args, in_shardings))
+        return _apply(fn(*args), out_shardings)
+
+    return wrapped

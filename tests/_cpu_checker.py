@@ -1,0 +1,61 @@
+"""TEST INFRASTRUCTURE: a stand-in for ``capi`` (same function names and semantics) built on the
+CPU oracle, so that the collective PLANS of the host layer can be exercised on a GPU-less box
+(virtual runtime on cpu, gloo world_size 2).  The product never imports this."""
+import torch
+
+from oracle import reference_math as rm
+
+BF16, F32 = torch.bfloat16, torch.float32
+EPI_NONE, EPI_BIAS, EPI_BIAS_RELU, EPI_BIAS_GELU_TANH, EPI_RELU, EPI_GELU_TANH = range(6)
+B_KN, B_NK = 0, 1
+
+
+def _r(x):
+    return x.to(BF16).to(F32)
+
+
+def gemm_bf16(a, b, *, b_layout=B_KN, bias=None, epilogue=EPI_NONE, out=None, out_dtype=BF16):
+    bb = b.to(F32) if b_layout == B_KN else b.to(F32).t()
+    acc = a.to(F32) @ bb
+    if out_dtype == F32 and epilogue == EPI_NONE:
+        res = acc
+    else:
+        v = _r(acc)
+        if epilogue in (EPI_BIAS, EPI_BIAS_RELU, EPI_BIAS_GELU_TANH):
+            v = _r(v + bias.to(F32))
+        if epilogue in (EPI_BIAS_RELU, EPI_RELU):
+            v = torch.relu(v)
+        if epilogue in (EPI_BIAS_GELU_TANH, EPI_GELU_TANH):
+            v = _r(rm.gelu_tanh(v))
+        res = v.to(out_dtype)
+    if out is not None:
+        out.copy_(res)
+        return out
+    return res
+
+
+def gemm_f32(a, b, *, out=None, accumulate=False):
+    res = (a.double() @ b.double()).float()
+    if out is not None:
+        out.copy_(out + res if accumulate else res)
+        return out
+    return res
+
+
+def attention_fwd(q, k, v, *, scale=None, causal=False, out=None):
+    return rm.attention_core(q, k, v, scale, causal)
+
+
+def cast_f32_to_bf16(src, out=None):
+    return src.to(BF16)
+
+
+def cast_bf16_to_f32(src, out=None):
+    return src.to(F32)
+
+
+def sum_partials_to_bf16(partials, bias=None, out=None):
+    v = _r(partials.sum(dim=0))
+    if bias is not None:
+        v = _r(v + bias.to(F32))
+    return v.to(BF16)

@@ -130,6 +130,41 @@ def main():
             good = torch.allclose(out.double(), want, rtol=1e-5, atol=1e-5 * K ** 0.5)
             print(f"  f32 B={Bt} M={M} N={N} K={K}: max_rel={err:.3e} {'OK' if good else 'FAIL'}", flush=True)
             ok &= good
+    elif args.what == "attn":
+        sys.path.insert(0, ROOT)
+        from oracle import reference_math as rm
+        for (B, Sq, Sk, H, D, causal) in [(1, 128, 128, 1, 64, False), (1, 128, 128, 1, 128, False),
+                                          (1, 128, 256, 1, 128, False), (2, 256, 512, 2, 128, False),
+                                          (1, 384, 384, 2, 64, True), (1, 200, 333, 2, 128, False),
+                                          (1, 1024, 1024, 2, 128, True)]:
+            q = rm.synthetic((B, Sq, H, D), 1).to(torch.bfloat16)
+            k = rm.synthetic((B, Sk, H, D), 2).to(torch.bfloat16)
+            v = rm.synthetic((B, Sk, H, D), 3).to(torch.bfloat16)
+            o = capi.attention_fwd(q.cuda(), k.cuda(), v.cuda(), causal=causal)
+            torch.cuda.synchronize()
+            want = rm.attention_core(q, k, v, causal=causal).float()
+            err = (o.cpu().float() - want).abs()
+            bad = (err > 2e-2 * want.abs() + 2e-2)
+            print(f"  attn B={B} Sq={Sq} Sk={Sk} H={H} D={D} causal={causal}: max_abs={err.max().item():.3e} "
+                  f"bad={bad.sum().item()}/{bad.numel()} {'OK' if not bad.any() else 'FAIL'}", flush=True)
+            if bad.any():
+                rows = bad.any(dim=3).any(dim=2).any(dim=0).nonzero().flatten()
+                cols = bad.any(dim=2).any(dim=1).any(dim=0).nonzero().flatten()
+                print(f"    bad query rows n={rows.numel()} first={rows[:8].tolist()}; bad d n={cols.numel()} "
+                      f"first={cols[:8].tolist()}; got[0,0,0,:4]={o[0,0,0,:4].tolist()} want={want[0,0,0,:4].tolist()}")
+                ok = False
+    elif args.what == "attn_time":
+        for (B, S, H, D, causal) in [(8, 4096, 32, 128, False), (8, 4096, 32, 128, True), (4, 8192, 32, 128, True),
+                                     (8, 4096, 32, 64, False)]:
+            q, k, v = (torch.randn(B, S, H, D, device="cuda").to(torch.bfloat16) for _ in range(3))
+            o = torch.empty_like(q)
+            ms = time_fn(lambda: capi.attention_fwd(q, k, v, causal=causal, out=o), iters=5, warmup=2)
+            fl = (2.0 * B * H * S * (S + 1) * D) if causal else 4.0 * B * H * S * S * D
+            print(f"  attn B={B} S={S} H={H} D={D} causal={causal}: {ms:.3f} ms {fl / ms / 1e9:.1f} TFLOP/s", flush=True)
+            qt, kt, vt = (t.transpose(1, 2) for t in (q, k, v))
+            ms = time_fn(lambda: torch.nn.functional.scaled_dot_product_attention(qt, kt, vt, is_causal=causal), iters=5,
+                         warmup=2)
+            print(f"    torch sdpa: {ms:.3f} ms {fl / ms / 1e9:.1f} TFLOP/s", flush=True)
     else:
         raise SystemExit(f"unknown check {args.what}")
     print("RESULT", "PASS" if ok else "FAIL", flush=True)
