@@ -217,7 +217,9 @@ class FFNBench:
         self.copy_in = torch.cuda.Stream(device=dev)
         self.copy_out = torch.cuda.Stream(device=dev)
         self._events = []
-        self._pending = None
+        self.e2e_chunks = 8
+        self._in_ev = [torch.cuda.Event() for _ in range(self.e2e_chunks)]
+        self._out_ev = [torch.cuda.Event() for _ in range(self.e2e_chunks)]
 
     def parallelism_name(self):
         if self.mode == "single":
@@ -249,15 +251,38 @@ class FFNBench:
 
     # --- end-to-end step: host x -> device -> FFN -> host y
     def step_e2e(self):
+        """The public host-buffer call: x arrives in pinned host memory, y is returned in pinned host
+        memory.  On one GPU the tokens go through in chunks so that the H2D copy of chunk c+1, the two
+        GEMMs of chunk c and the D2H copy of chunk c-1 overlap (PCIe is full duplex)."""
         main = torch.cuda.current_stream(self.dev)
+        if self.world > 1:
+            self.copy_in.wait_stream(main)
+            with torch.cuda.stream(self.copy_in):
+                self.x_stage.copy_(self.x_host, non_blocking=True)
+            main.wait_stream(self.copy_in)
+            y = self.layer.forward(self.x_stage)
+            self.copy_out.wait_stream(main)
+            with torch.cuda.stream(self.copy_out):
+                self.y_host.copy_(y, non_blocking=True)
+            main.wait_stream(self.copy_out)
+            return self.y_host
+        layer, C = self.layer, self.e2e_chunks
+        rows = self.T // C
         self.copy_in.wait_stream(main)
-        with torch.cuda.stream(self.copy_in):
-            self.x_stage.copy_(self.x_host, non_blocking=True)
-        main.wait_stream(self.copy_in)
-        y = self.layer.forward(self.x_stage)
         self.copy_out.wait_stream(main)
-        with torch.cuda.stream(self.copy_out):
-            self.y_host.copy_(y, non_blocking=True)
+        for c in range(C):
+            sl = slice(c * rows, (c + 1) * rows)
+            with torch.cuda.stream(self.copy_in):
+                self.x_stage[sl].copy_(self.x_host[sl], non_blocking=True)
+                self._in_ev[c].record(self.copy_in)
+            main.wait_event(self._in_ev[c])
+            capi.gemm_bf16(self.x_stage[sl], layer.w1, bias=layer.b1, epilogue=layer.act, out=layer.h[sl])
+            capi.gemm_bf16(layer.h[sl], layer.w2, bias=layer.b2,
+                           epilogue=capi.EPI_BIAS if layer.b2 is not None else capi.EPI_NONE, out=layer.y[sl])
+            self._out_ev[c].record(main)
+            with torch.cuda.stream(self.copy_out):
+                self.copy_out.wait_event(self._out_ev[c])
+                self.y_host[sl].copy_(layer.y[sl], non_blocking=True)
         main.wait_stream(self.copy_out)
         return self.y_host
 

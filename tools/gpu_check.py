@@ -153,6 +153,11 @@ def main():
                 print(f"    bad query rows n={rows.numel()} first={rows[:8].tolist()}; bad d n={cols.numel()} "
                       f"first={cols[:8].tolist()}; got[0,0,0,:4]={o[0,0,0,:4].tolist()} want={want[0,0,0,:4].tolist()}")
                 ok = False
+    elif args.what == "attn_prof":
+        q, k, v = (torch.randn(2, 4096, 16, 128, device="cuda").to(torch.bfloat16) for _ in range(3))
+        for _ in range(3):
+            capi.attention_fwd(q, k, v)
+        torch.cuda.synchronize()
     elif args.what == "attn_time":
         for (B, S, H, D, causal) in [(8, 4096, 32, 128, False), (8, 4096, 32, 128, True), (4, 8192, 32, 128, True),
                                      (8, 4096, 32, 64, False)]:
