@@ -131,6 +131,29 @@ int b200_attention_fwd(const void* Q, const void* K, const void* V, void* O, int
 int b200_ffn_fwd(const void* x, const void* W1, const void* b1, const void* W2, const void* b2, void* h, void* y,
                  int y_dtype, int T, int d_model, int F, int act, void* stream);
 
+/*
+ * b200_ffn_fwd for hosts that cannot allocate device memory around the call.  (This entry point
+ * has no counterpart in the reference; it exists for integrators of this library.)
+ * Who needs it: a custom-call handler running under a framework whose own allocator has already
+ * taken almost all of HBM (XLA preallocates it), where a cudaMalloc for the intermediate h either
+ * fails or forces a device-wide synchronisation, and bindings whose operand list was fixed without
+ * a scratch buffer.  Same arguments and result as b200_ffn_fwd minus `h`: the intermediate lives in
+ * a 32 MiB array compiled into the library (B200_FFN_STATIC_SCRATCH_BYTES), so the call performs no
+ * cudaMalloc / cudaFree and no allocating library call.
+ *  - Limit: 2 * T * F bytes must fit in 32 MiB (e.g. T = 1024 tokens at F = 16384); larger requests
+ *    return B200_ERR_INVALID_ARGUMENT with the sizes in b200_last_error() -- split the tokens.
+ *  - Every GPU whose context loads the library carries those 32 MiB until the process exits.
+ *  - The first call on each device looks up the array's device address (once, with that device
+ *    current); make that first call before starting any stream capture.
+ *  - All calls on a device share the one array and it keeps whatever the previous call wrote;
+ *    nothing needs clearing because the first GEMM overwrites all of h that the second reads.
+ *    Two calls that overlap on the GPU (different streams, or host threads racing on one device)
+ *    would both write it and corrupt each other: keep calls on a device stream-ordered.
+ */
+#define B200_FFN_STATIC_SCRATCH_BYTES (32ull << 20)
+int b200_ffn_fwd_static_scratch(const void* x, const void* W1, const void* b1, const void* W2, const void* b2, void* y,
+                                int y_dtype, int T, int d_model, int F, int act, void* stream);
+
 /* dst[i] = bf16(src[i]) -- the per-call f32->bf16 parameter/activation cast flax
  * promote_dtype performs inside nn.Dense (case6_attention.py:61-90). n elements. */
 int b200_cast_f32_to_bf16(const float* src, void* dst, int64_t n, void* stream);
