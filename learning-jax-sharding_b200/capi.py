@@ -69,7 +69,9 @@ def load():
     lib.b200_cast_bf16_to_f32.argtypes = [vp, vp, i64, vp]
     lib.b200_sum_partials_to_bf16.argtypes = [vp, i64, i32, vp, i64, vp, i64, vp]
     lib.b200_gemm_set_tuning.argtypes = [i32, i32]
-    for name in EXPORTED_SYMBOLS[3:] + ("b200_gemm_set_tuning",):
+    lib.b200_attention_set_variant.argtypes = [i32]
+    lib.b200_gemm_set_group_m.argtypes = [i32]
+    for name in EXPORTED_SYMBOLS[3:] + ("b200_gemm_set_tuning", "b200_attention_set_variant", "b200_gemm_set_group_m"):
         getattr(lib, name).restype = i32
     _lib = lib
     return lib
@@ -105,6 +107,16 @@ def launch_count() -> int:
 def set_gemm_tuning(cta_group: int = 0, block_n: int = 0):
     """Force the GEMM tile configuration (0 = library heuristic). For tests and tuning runs."""
     _check(load().b200_gemm_set_tuning(cta_group, block_n), "b200_gemm_set_tuning")
+
+
+def set_gemm_group_m(group_m: int = 8):
+    """Tile rasterisation group size (row-blocks that sweep the columns together). Tuning hook."""
+    _check(load().b200_gemm_set_group_m(group_m), "b200_gemm_set_group_m")
+
+
+def set_attention_variant(variant: int = 0):
+    """0 = library heuristic, 1 = one 128-row query tile per CTA, 2 = two tiles per CTA (ping-pong)."""
+    _check(load().b200_attention_set_variant(variant), "b200_attention_set_variant")
 
 
 def gemm_bf16(a, b, *, b_layout=B_KN, bias=None, epilogue=EPI_NONE, out=None, out_dtype=torch.bfloat16,

@@ -307,7 +307,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
   }
 }
 
-static int make_bsnh_map(CUtensorMap* tm, const void* base, int B, int S, int H, int D, int64_t sb, int64_t ss,
+int make_bsnh_map(CUtensorMap* tm, const void* base, int B, int S, int H, int D, int64_t sb, int64_t ss,
                          int64_t sh, int rows) {
   uint64_t dims[4] = {static_cast<uint64_t>(D), static_cast<uint64_t>(H), static_cast<uint64_t>(S),
                       static_cast<uint64_t>(B)};
@@ -337,9 +337,19 @@ static int launch_attention(const void* Q, const void* K, const void* V, const A
   return B200_OK;
 }
 
+int attention_fwd2_dispatch(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
+                            const int64_t* strides, float scale, int causal, cudaStream_t stream);
+static int g_attn_variant = 0;   // 0 = auto, 1 = one query tile per CTA, 2 = two query tiles per CTA
+
 }  // namespace b200
 
 using namespace b200;
+
+extern "C" int b200_attention_set_variant(int variant) {
+  if (variant < 0 || variant > 2) return fail(B200_ERR_INVALID_ARGUMENT, "attention variant must be 0, 1 or 2");
+  g_attn_variant = variant;
+  return B200_OK;
+}
 
 extern "C" int b200_attention_fwd(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H,
                                   int D, int64_t q_stride_b, int64_t q_stride_s, int64_t q_stride_h,
@@ -358,6 +368,9 @@ extern "C" int b200_attention_fwd(const void* Q, const void* K, const void* V, v
   B200_REQUIRE((reinterpret_cast<uintptr_t>(Q) | reinterpret_cast<uintptr_t>(K) | reinterpret_cast<uintptr_t>(V) |
                 reinterpret_cast<uintptr_t>(O)) % 16 == 0,
                "b200_attention_fwd: operands must be 16-byte aligned");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const bool two_tiles = g_attn_variant == 2 || (g_attn_variant == 0 && Sq > kAttnBM);
+  if (two_tiles) return attention_fwd2_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
   AttnParams p = {};
   p.O = reinterpret_cast<__nv_bfloat16*>(O);
   p.B = B;
@@ -370,7 +383,6 @@ extern "C" int b200_attention_fwd(const void* Q, const void* K, const void* V, v
   p.scale_log2 = scale * 1.4426950408889634f;
   p.causal = causal ? 1 : 0;
   p.num_q_tiles = (Sq + kAttnBM - 1) / kAttnBM;
-  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (D == 64) return launch_attention<64>(Q, K, V, p, B, Sq, Sk, H, strides, strides + 3, strides + 6, st);
   return launch_attention<128>(Q, K, V, p, B, Sq, Sk, H, strides, strides + 3, strides + 6, st);
 }

@@ -1,0 +1,386 @@
+// Attention forward, two query tiles per CTA ("ping-pong"): the variant used whenever a (batch, head)
+// has at least two 128-row query tiles.  Same math and layout as attention.cu (reference order
+// case6_attention.py:121-135: f32 scores, f32 softmax, bf16 P, f32-accumulated P.V, bf16 out).
+//
+// One CTA = one (batch, head, 256-query block) = two 128-row tiles q in {0,1}; 12 warps:
+//   warp 0        TMA producer: both Q tiles once, then K_0,V_0,K_1,V_1,... through one smem ring
+//   warp 1        MMA issuer: polls which of {Q.K^T(q,j), P.V(q,j)} is ready and issues it, so the
+//                 tensor pipe serves one tile while the other tile's softmax warps are busy
+//   warp 2        TMEM allocator (S0,S1: 2 x 128 columns; O0,O1: 2 x D columns)
+//   warps 4..7    softmax / correction / epilogue of query tile 0 (one row per thread)
+//   warps 8..11   the same for query tile 1
+// A softmax thread pulls its whole 128-wide score row out of TMEM in one go and releases S at once
+// (s_free), so Q.K^T of the next KV tile overlaps the exp pass of the current one.
+#include <cuda.h>
+#include <math.h>
+
+#include "host_common.h"
+#include "sm100_ptx.cuh"
+
+namespace b200 {
+
+constexpr int kA2BM = 128;      // rows per query tile
+constexpr int kA2BN = 128;      // keys per KV tile
+constexpr int kA2Threads = 384;
+constexpr float kA2Rescale = 8.0f;
+
+template <int D>
+struct Attn2Cfg {
+  static constexpr int kQBytes = kA2BM * D * 2;          // one query tile
+  static constexpr int kKVBytes = kA2BN * D * 2;         // one K or V tile
+  static constexpr int kPBytes = kA2BM * kA2BN * 2;      // one P tile
+  static constexpr int kBudget = 227 * 1024 - 1024 - 512 - 2 * kQBytes - 2 * kPBytes;
+  static constexpr int kStages = kBudget / kKVBytes > 6 ? 6 : kBudget / kKVBytes;
+  static constexpr int kSmemBytes = 2 * kQBytes + 2 * kPBytes + kStages * kKVBytes + 1024 + 512;
+  static constexpr int kTmemCols = 512;
+  static constexpr int kSCol = 0;       // S[q] at kSCol + 128 q
+  static constexpr int kOCol = 256;     // O[q] at kOCol + 128 q
+};
+
+struct Attn2Params {
+  __nv_bfloat16* O;
+  int Sq, Sk;
+  int64_t o_stride_b, o_stride_s, o_stride_h;
+  float scale_log2;
+  int causal;
+  int num_q_blocks;
+};
+
+__device__ __forceinline__ float max3(float a, float b, float c) {
+  float r;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+  return r;
+}
+
+template <int D>
+__global__ void __launch_bounds__(kA2Threads, 1)
+attention_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                      const __grid_constant__ CUtensorMap tmV, const Attn2Params p) {
+  using Cfg = Attn2Cfg<D>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;                                   // [2][128][D]
+  uint8_t* sP = sQ + 2 * Cfg::kQBytes;                  // [2][128][128]
+  uint8_t* sKV = sP + 2 * Cfg::kPBytes;                 // ring
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sKV + Cfg::kStages * Cfg::kKVBytes);
+  uint64_t* q_full = bars;                              // 1
+  uint64_t* kv_full = bars + 1;                         // kStages
+  uint64_t* kv_empty = kv_full + Cfg::kStages;          // kStages (2 arrivals: one per query tile)
+  uint64_t* s_full = kv_empty + Cfg::kStages;           // 2
+  uint64_t* s_free = s_full + 2;                        // 2 (4 warp arrivals)
+  uint64_t* p_full = s_free + 2;                        // 2 (4 warp arrivals)
+  uint64_t* pv_done = p_full + 2;                       // 2
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(pv_done + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int q_block = p.causal ? (p.num_q_blocks - 1 - blockIdx.x) : blockIdx.x;   // heaviest first
+  const int head = blockIdx.y;
+  const int batch = blockIdx.z;
+  const int f_base = q_block * 2 * kA2BM;
+  const int off = p.Sk - p.Sq;
+  // KV tiles each query tile needs (0 if the tile lies beyond Sq)
+  int n_tiles[2];
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    const int f0 = f_base + q * kA2BM;
+    int kv_len = p.Sk;
+    if (p.causal) kv_len = min(p.Sk, f0 + kA2BM + off);
+    n_tiles[q] = f0 < p.Sq ? (kv_len + kA2BN - 1) / kA2BN : 0;
+  }
+  const int n_max = max(n_tiles[0], n_tiles[1]);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmK);
+    tma_prefetch_desc(&tmV);
+  }
+  if (warp == 1 && lane == 0) {
+    mbar_init(q_full, 1);
+    for (int s = 0; s < Cfg::kStages; ++s) {
+      mbar_init(&kv_full[s], 1);
+      mbar_init(&kv_empty[s], 2);
+    }
+    for (int q = 0; q < 2; ++q) {
+      mbar_init(&s_full[q], 1);
+      mbar_init(&s_free[q], 4);
+      mbar_init(&p_full[q], 4);
+      mbar_init(&pv_done[q], 1);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc<Cfg::kTmemCols>(tmem_ptr_smem);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  // register re-split: the control warp group needs few, each softmax thread keeps a 128-wide score row
+  if (warp < 4) {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+  if (warp == 0 && lane == 0) {
+    // ===================== TMA producer =====================
+    mbar_arrive_expect_tx(q_full, 2 * Cfg::kQBytes);
+#pragma unroll
+    for (int q = 0; q < 2; ++q)
+#pragma unroll
+      for (int c = 0; c < D / 64; ++c)
+        tma_load_4d(sQ + q * Cfg::kQBytes + c * (kA2BM * 128), &tmQ, q_full, c * 64, head, f_base + q * kA2BM, batch);
+    // ring item i: K_j for i = 2j, V_j for i = 2j+1
+    for (int i = 0; i < 2 * n_max; ++i) {
+      const int st = i % Cfg::kStages;
+      const uint32_t ph = (i / Cfg::kStages) & 1;
+      const int t0 = (i >> 1) * kA2BN;
+      mbar_wait(&kv_empty[st], ph ^ 1);
+      mbar_arrive_expect_tx(&kv_full[st], Cfg::kKVBytes);
+      const CUtensorMap* tm = (i & 1) ? &tmV : &tmK;
+#pragma unroll
+      for (int c = 0; c < D / 64; ++c)
+        tma_load_4d(sKV + st * Cfg::kKVBytes + c * (kA2BN * 128), tm, &kv_full[st], c * 64, head, t0, batch);
+    }
+  } else if (warp == 1 && lane == 0) {
+    // ===================== MMA issuer =====================
+    constexpr uint32_t idesc_qk = make_idesc_bf16(kA2BM, kA2BN, false, false);
+    constexpr uint32_t idesc_pv = make_idesc_bf16(kA2BM, D, false, true);
+    int next_qk[2] = {0, 0};     // next KV tile whose Q.K^T is to be issued, per query tile
+    int next_pv[2] = {0, 0};
+    mbar_wait(q_full, 0);
+    int remaining = 2 * (n_tiles[0] + n_tiles[1]);
+    uint32_t idle = 0;
+    while (remaining > 0) {
+      bool progressed = false;
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        // ---- S[q] = Q_q . K_j^T
+        if (next_qk[q] < n_tiles[q]) {
+          const int j = next_qk[q];
+          const int i = 2 * j, st = i % Cfg::kStages;
+          const uint32_t ph = (i / Cfg::kStages) & 1;
+          const bool s_ok = (j == 0) || mbar_try_wait(&s_free[q], (j - 1) & 1);
+          if (s_ok && mbar_try_wait(&kv_full[st], ph)) {
+            tc_fence_after();
+            const uint32_t q_addr = smem_u32(sQ + q * Cfg::kQBytes);
+            const uint32_t k_addr = smem_u32(sKV + st * Cfg::kKVBytes);
+            const uint32_t s_tmem = tmem_base + Cfg::kSCol + q * 128;
+#pragma unroll
+            for (int kk = 0; kk < D / 16; ++kk) {
+              const uint32_t o = (kk >> 2) * (kA2BM * 128) + (kk & 3) * 32;
+              mma_bf16_ss(s_tmem, make_smem_desc_sw128(q_addr + o, 16, 1024),
+                          make_smem_desc_sw128(k_addr + o, 16, 1024), idesc_qk, kk > 0 ? 1u : 0u);
+            }
+            mma_commit(&s_full[q]);
+            mma_commit(&kv_empty[st]);
+            if (j >= n_tiles[q ^ 1]) mbar_arrive(&kv_empty[st]);   // the other tile never reads K_j
+            ++next_qk[q];
+            --remaining;
+            progressed = true;
+          }
+        }
+        // ---- O[q] += P_q . V_j
+        if (next_pv[q] < next_qk[q]) {
+          const int j = next_pv[q];
+          const int i = 2 * j + 1, st = i % Cfg::kStages;
+          const uint32_t ph = (i / Cfg::kStages) & 1;
+          if (mbar_try_wait(&p_full[q], j & 1) && mbar_try_wait(&kv_full[st], ph)) {
+            tc_fence_after();
+            const uint32_t p_addr = smem_u32(sP + q * Cfg::kPBytes);
+            const uint32_t v_addr = smem_u32(sKV + st * Cfg::kKVBytes);
+            const uint32_t o_tmem = tmem_base + Cfg::kOCol + q * 128;
+#pragma unroll
+            for (int kk = 0; kk < kA2BN / 16; ++kk) {
+              const uint64_t da =
+                  make_smem_desc_sw128(p_addr + (kk >> 2) * (kA2BM * 128) + (kk & 3) * 32, 16, 1024);
+              const uint64_t db = make_smem_desc_sw128(v_addr + kk * (16 * 128), kA2BN * 128, 1024);
+              mma_bf16_ss(o_tmem, da, db, idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
+            }
+            mma_commit(&pv_done[q]);
+            mma_commit(&kv_empty[st]);
+            if (j >= n_tiles[q ^ 1]) mbar_arrive(&kv_empty[st]);
+            ++next_pv[q];
+            --remaining;
+            progressed = true;
+          }
+        }
+      }
+#if B200_WATCHDOG
+      if (progressed) {
+        idle = 0;
+      } else if (++idle > (1u << 26)) {
+        printf("b200: attention MMA scheduler stuck block=(%d,%d,%d) qk=(%d,%d) pv=(%d,%d)\n", (int)blockIdx.x,
+               (int)blockIdx.y, (int)blockIdx.z, next_qk[0], next_qk[1], next_pv[0], next_pv[1]);
+        __trap();
+      }
+#endif
+    }
+  }
+  } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");
+    // ===================== softmax / correction / epilogue =====================
+    const int q = (warp - 4) >> 2;               // query tile of this warp group
+    const int quad = warp & 3;                   // TMEM lane quadrant
+    const int row = quad * 32 + lane;
+    const int f = f_base + q * kA2BM + row;
+    const int nt = n_tiles[q];
+    const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
+    const uint32_t s_tmem = lane_base + Cfg::kSCol + q * 128;
+    const uint32_t o_tmem = lane_base + Cfg::kOCol + q * 128;
+    uint8_t* sPq = sP + q * Cfg::kPBytes;
+    float m_used = -INFINITY;
+    float l_sum = 0.f;
+    for (int j = 0; j < nt; ++j) {
+      const int t0 = j * kA2BN;
+      int limit = p.Sk - t0;
+      if (p.causal) limit = min(limit, f + off + 1 - t0);
+      const bool need_mask = limit < kA2BN;
+      mbar_wait(&s_full[q], j & 1);
+      tc_fence_after();
+      // whole score row -> registers, then S[q] is free for Q.K^T of the next KV tile
+      uint32_t s[128];
+      {
+        uint32_t(&s0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[0]);
+        uint32_t(&s1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[32]);
+        uint32_t(&s2)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[64]);
+        uint32_t(&s3)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[96]);
+        tmem_ld_32x32(s_tmem, s0);
+        tmem_ld_32x32(s_tmem + 32, s1);
+        tmem_ld_32x32(s_tmem + 64, s2);
+        tmem_ld_32x32(s_tmem + 96, s3);
+        tmem_wait_ld();
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&s_free[q]);
+      if (need_mask) {
+#pragma unroll
+        for (int i = 0; i < 128; ++i)
+          if (i >= limit) s[i] = 0xff800000u;    // -inf
+      }
+      float mx = -INFINITY;
+#pragma unroll
+      for (int i = 0; i < 128; i += 2) mx = max3(mx, __uint_as_float(s[i]), __uint_as_float(s[i + 1]));
+      const float m_tile = mx * p.scale_log2;
+      float factor = 1.0f;
+      bool rescale = false;
+      if (j == 0) {
+        m_used = m_tile;
+      } else if (m_tile > m_used + kA2Rescale) {
+        factor = exp2_approx(m_used - m_tile);
+        m_used = m_tile;
+        rescale = true;
+      }
+      // P[q] buffer is free and O[q] is stable once P.V of tile j-1 has completed
+      if (j > 0) {
+        mbar_wait(&pv_done[q], (j - 1) & 1);
+        tc_fence_after();
+      }
+      if (__any_sync(0xffffffffu, rescale)) {
+        l_sum *= factor;
+#pragma unroll 1
+        for (int c = 0; c < D / 32; ++c) {
+          uint32_t r[32];
+          tmem_ld_32x32(o_tmem + c * 32, r);
+          tmem_wait_ld();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * factor);
+          tmem_st_32x32(o_tmem + c * 32, r);
+        }
+        tmem_wait_st();
+      }
+      const float neg_m = -m_used;
+      float sum0 = 0.f, sum1 = 0.f;
+#pragma unroll
+      for (int u = 0; u < 16; ++u) {            // 16-byte unit u = keys [8u, 8u+8)
+        uint32_t pk[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float p0 = exp2_approx(fmaf(__uint_as_float(s[u * 8 + 2 * e]), p.scale_log2, neg_m));
+          const float p1 = exp2_approx(fmaf(__uint_as_float(s[u * 8 + 2 * e + 1]), p.scale_log2, neg_m));
+          sum0 += p0;
+          sum1 += p1;
+          pk[e] = pack_bf16x2(p0, p1);
+        }
+        const int chunk = u >> 3;
+        uint8_t* dst = sPq + chunk * (kA2BM * 128) + row * 128 + (((u & 7) ^ (row & 7)) << 4);
+        *reinterpret_cast<uint4*>(dst) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+      }
+      l_sum += sum0 + sum1;
+      fence_async_smem();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&p_full[q]);
+    }
+    if (nt > 0) {
+      mbar_wait(&pv_done[q], (nt - 1) & 1);
+      tc_fence_after();
+      const float inv_l = 1.0f / l_sum;
+      __nv_bfloat16* dst = p.O + batch * p.o_stride_b + static_cast<int64_t>(f) * p.o_stride_s + head * p.o_stride_h;
+#pragma unroll 1
+      for (int c = 0; c < D / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(o_tmem + c * 32, r);
+        tmem_wait_ld();
+        if (f < p.Sq) {
+#pragma unroll
+          for (int i = 0; i < 32; i += 8) {
+            uint4 o;
+            o.x = pack_bf16x2(__uint_as_float(r[i]) * inv_l, __uint_as_float(r[i + 1]) * inv_l);
+            o.y = pack_bf16x2(__uint_as_float(r[i + 2]) * inv_l, __uint_as_float(r[i + 3]) * inv_l);
+            o.z = pack_bf16x2(__uint_as_float(r[i + 4]) * inv_l, __uint_as_float(r[i + 5]) * inv_l);
+            o.w = pack_bf16x2(__uint_as_float(r[i + 6]) * inv_l, __uint_as_float(r[i + 7]) * inv_l);
+            *reinterpret_cast<uint4*>(dst + c * 32 + i) = o;
+          }
+        }
+      }
+    }
+  }
+
+  __syncwarp();
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+  }
+}
+
+int make_bsnh_map(CUtensorMap* tm, const void* base, int B, int S, int H, int D, int64_t sb, int64_t ss, int64_t sh,
+                  int rows);
+
+template <int D>
+static int launch_attention2(const void* Q, const void* K, const void* V, const Attn2Params& p, int B, int Sq, int Sk,
+                             int H, const int64_t* qs, const int64_t* ks, const int64_t* vs, cudaStream_t stream) {
+  using Cfg = Attn2Cfg<D>;
+  static_assert(Cfg::kStages >= 3, "KV ring needs at least three stages");
+  CUtensorMap tmQ, tmK, tmV;
+  int rc = make_bsnh_map(&tmQ, Q, B, Sq, H, D, qs[0], qs[1], qs[2], kA2BM);
+  if (rc != B200_OK) return rc;
+  rc = make_bsnh_map(&tmK, K, B, Sk, H, D, ks[0], ks[1], ks[2], kA2BN);
+  if (rc != B200_OK) return rc;
+  rc = make_bsnh_map(&tmV, V, B, Sk, H, D, vs[0], vs[1], vs[2], kA2BN);
+  if (rc != B200_OK) return rc;
+  auto kern = attention_fwd2_kernel<D>;
+  B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+  dim3 grid(p.num_q_blocks, H, B);
+  kern<<<grid, kA2Threads, Cfg::kSmemBytes, stream>>>(tmQ, tmK, tmV, p);
+  B200_CUDA_CHECK(cudaGetLastError());
+  launch_counter().fetch_add(1);
+  return B200_OK;
+}
+
+int attention_fwd2_dispatch(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
+                            const int64_t* strides, float scale, int causal, cudaStream_t stream) {
+  Attn2Params p = {};
+  p.O = reinterpret_cast<__nv_bfloat16*>(O);
+  p.Sq = Sq;
+  p.Sk = Sk;
+  p.o_stride_b = strides[9];
+  p.o_stride_s = strides[10];
+  p.o_stride_h = strides[11];
+  p.scale_log2 = scale * 1.4426950408889634f;
+  p.causal = causal ? 1 : 0;
+  p.num_q_blocks = (Sq + 2 * kA2BM - 1) / (2 * kA2BM);
+  if (D == 64) return launch_attention2<64>(Q, K, V, p, B, Sq, Sk, H, strides, strides + 3, strides + 6, stream);
+  return launch_attention2<128>(Q, K, V, p, B, Sq, Sk, H, strides, strides + 3, strides + 6, stream);
+}
+
+}  // namespace b200

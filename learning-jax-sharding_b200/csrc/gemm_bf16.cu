@@ -23,7 +23,6 @@ constexpr int kBM = 128;        // rows of C per CTA (TMEM lanes)
 constexpr int kBK = 64;         // K elements per pipeline stage = one 128-byte swizzle row
 constexpr int kUmmaK = 16;      // K per tcgen05.mma for 16-bit inputs
 constexpr int kGemmThreads = 256;
-constexpr int kGroupM = 8;      // tile rasterisation: kGroupM row-blocks share B panels in L2
 
 template <int BN, int G>
 struct GemmCfg {
@@ -49,6 +48,7 @@ struct GemmParams {
   // optional row-blocked view of A: logical row m lives at physical row
   // (m / a_rows_per_block) * a_block_stride + m % a_rows_per_block   (0 = plain row-major)
   int a_rows_per_block, a_block_stride;
+  int group_m;   // tile rasterisation: group_m row-blocks sweep all column-blocks together (L2 reuse)
 };
 
 __device__ __forceinline__ float gelu_tanh_f(float x) {
@@ -68,11 +68,12 @@ __device__ __forceinline__ float apply_epilogue(float acc, float bias, int epi, 
   return v;
 }
 
-__device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, int& m_blk, int& n_blk) {
-  const int per_group = kGroupM * tiles_n;
+__device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, int group_m, int& m_blk,
+                                            int& n_blk) {
+  const int per_group = group_m * tiles_n;
   const int group = tile / per_group;
-  const int first_m = group * kGroupM;
-  const int gsize = min(tiles_m - first_m, kGroupM);
+  const int first_m = group * group_m;
+  const int gsize = min(tiles_m - first_m, group_m);
   const int in_group = tile - group * per_group;
   m_blk = first_m + in_group % gsize;
   n_blk = in_group / gsize;
@@ -137,7 +138,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     uint32_t phase = 0;
     for (int tile = worker; tile < num_tiles; tile += num_workers) {
       int m_blk, n_blk;
-      tile_coords(tile, p.tiles_m, p.tiles_n, m_blk, n_blk);
+      tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, m_blk, n_blk);
       int m0 = (m_blk * G + cta_rank) * kBM;
       if (p.a_rows_per_block > 0) m0 = (m0 / p.a_rows_per_block) * p.a_block_stride + m0 % p.a_rows_per_block;
       const int n0 = n_blk * BN + cta_rank * Cfg::kBNcta;
@@ -219,7 +220,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const bool has_bias = p.bias != nullptr;
     for (int tile = worker; tile < num_tiles; tile += num_workers) {
       int m_blk, n_blk;
-      tile_coords(tile, p.tiles_m, p.tiles_n, m_blk, n_blk);
+      tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, m_blk, n_blk);
       const int row = (m_blk * G + cta_rank) * kBM + q * 32 + lane;
       const int n0 = n_blk * BN;
       mbar_wait(&tmem_full_bar[acc], acc_phase);
@@ -315,6 +316,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 // ------------------------------------------------------------------ host side
 static int g_force_cta_group = 0;   // 0 = heuristic; 1 / 2 force (set through b200_gemm_set_tuning)
 static int g_force_bn = 0;
+static int g_group_m = 8;
 
 template <int BN, int G, bool kBKmajor>
 static int launch_gemm(const void* A, int64_t lda, const void* B, int64_t ldb, const GemmParams& p0,
@@ -323,6 +325,7 @@ static int launch_gemm(const void* A, int64_t lda, const void* B, int64_t ldb, c
   GemmParams p = p0;
   p.tiles_m = (p.M + kBM * G - 1) / (kBM * G);
   p.tiles_n = (p.N + BN - 1) / BN;
+  p.group_m = g_group_m;
   CUtensorMap tmA, tmB;
   {
     uint64_t a_rows = static_cast<uint64_t>(p.M);
@@ -388,6 +391,12 @@ extern "C" int b200_gemm_set_tuning(int cta_group, int block_n) {
     return fail(B200_ERR_INVALID_ARGUMENT, "block_n must be 0, 64, 128 or 256");
   g_force_cta_group = cta_group;
   g_force_bn = block_n;
+  return B200_OK;
+}
+
+extern "C" int b200_gemm_set_group_m(int group_m) {
+  if (group_m < 1 || group_m > 1024) return fail(B200_ERR_INVALID_ARGUMENT, "group_m must be in [1, 1024]");
+  g_group_m = group_m;
   return B200_OK;
 }
 

@@ -24,8 +24,10 @@ def _dev(t, dtype=None):
 @pytest.fixture(autouse=True)
 def _default_tuning(ljs):
     ljs.capi.set_gemm_tuning(0, 0)
+    ljs.capi.set_attention_variant(0)
     yield
     ljs.capi.set_gemm_tuning(0, 0)
+    ljs.capi.set_attention_variant(0)
 
 
 # ---------------------------------------------------------------------------- fp32 matmuls
@@ -192,9 +194,12 @@ def test_attention_against_golden(ljs, d, causal):
 
 
 @pytest.mark.parametrize("shape", [(1, 1, 1, 1, 64), (1, 5, 300, 2, 64), (2, 128, 128, 3, 128), (1, 257, 257, 2, 128),
-                                   (2, 100, 1000, 2, 64), (1, 1024, 1024, 4, 128)])
+                                   (2, 100, 1000, 2, 64), (1, 1024, 1024, 4, 128), (1, 384, 640, 2, 128),
+                                   (1, 1300, 1300, 1, 64)])
 @pytest.mark.parametrize("causal", [False, True])
-def test_attention_ragged_shapes(ljs, shape, causal):
+@pytest.mark.parametrize("variant", [1, 2])
+def test_attention_ragged_shapes(ljs, shape, causal, variant):
+    ljs.capi.set_attention_variant(variant)      # 1 = one query tile per CTA, 2 = two tiles (ping-pong)
     B, Sq, Sk, H, D = shape
     q = rm.synthetic((B, Sq, H, D), 40).to(torch.bfloat16)
     k = rm.synthetic((B, Sk, H, D), 41).to(torch.bfloat16)

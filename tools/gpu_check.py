@@ -153,6 +153,20 @@ def main():
                 print(f"    bad query rows n={rows.numel()} first={rows[:8].tolist()}; bad d n={cols.numel()} "
                       f"first={cols[:8].tolist()}; got[0,0,0,:4]={o[0,0,0,:4].tolist()} want={want[0,0,0,:4].tolist()}")
                 ok = False
+    elif args.what == "gemm_group":
+        for (M, N, K) in [(16384, 16384, 4096), (16384, 4096, 16384)]:
+            a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
+            b = torch.randn(K, N, device="cuda").to(torch.bfloat16)
+            out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+            for g in (1, 2):
+                for gm in (2, 4, 8, 16, 32):
+                    capi.set_gemm_tuning(g, 256)
+                    capi.set_gemm_group_m(gm)
+                    ms = time_fn(lambda: capi.gemm_bf16(a, b, out=out), iters=30)
+                    print(f"  g={g} group_m={gm} M={M} N={N} K={K}: {ms:.3f} ms {2 * M * N * K / ms / 1e9:.1f} TFLOP/s",
+                          flush=True)
+            ms = time_fn(lambda: torch.matmul(a, b, out=out), iters=30)
+            print(f"  cublas M={M} N={N} K={K}: {ms:.3f} ms {2 * M * N * K / ms / 1e9:.1f} TFLOP/s", flush=True)
     elif args.what == "attn_prof":
         q, k, v = (torch.randn(2, 4096, 16, 128, device="cuda").to(torch.bfloat16) for _ in range(3))
         for _ in range(3):

@@ -1,0 +1,79 @@
+"""Multi-GPU bring-up (run under torchrun on the GPU box): the resident-weight sharded FFN layers
+against the CPU oracle on a reduced shape, rank by rank.
+
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29533 tools/mgpu_check.py
+"""
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import learning_jax_sharding_b200 as ljs  # noqa: E402
+from learning_jax_sharding_b200 import layers  # noqa: E402
+from oracle import reference_math as rm  # noqa: E402
+
+
+def main():
+    rt = ljs.init_distributed("nccl")
+    import torch.distributed as dist
+    rank, world = rt.rank, rt.world
+    dev = rt.torch_device
+    T, d, f = 4096, 1024, 4096
+    x = rm.synthetic((T, d), 0)
+    w1, b1 = rm.synthetic((d, f), 1, "weight"), rm.synthetic((f,), 2, "bias")
+    w2, b2 = rm.synthetic((f, d), 3, "weight"), rm.synthetic((d,), 4, "bias")
+    want = rm.ffn_forward(x, w1, b1, w2, b2, "gelu_tanh").float()
+    bf = lambda t: t.to(torch.bfloat16).to(dev)
+    ok = True
+    # tensor parallel: W1 columns / W2 rows over the ranks, reduce-scatter to sequence blocks
+    fl = f // world
+    for chunks in (1, 4):
+        tp = layers.TensorParallelFFN(bf(w1[:, rank * fl:(rank + 1) * fl].contiguous()), bf(b1[rank * fl:(rank + 1) * fl]),
+                                      bf(w2[rank * fl:(rank + 1) * fl].contiguous()), bf(b2), "gelu_tanh", T,
+                                      dist.group.WORLD, chunks=chunks)
+        for it in range(2):
+            y = tp.forward(bf(x))
+        torch.cuda.synchronize()
+        blk = T // world
+        err = (y.cpu().float() - want[rank * blk:(rank + 1) * blk]).abs()
+        good = bool((err <= 2e-2 * want[rank * blk:(rank + 1) * blk].abs() + 2e-2).all())
+        print(f"[rank {rank}] TP chunks={tp.chunks}: max_abs={err.max().item():.3e} {'OK' if good else 'FAIL'}", flush=True)
+        ok &= good
+    # FSDP: tokens over ranks, weights dim0-sharded, all-gather in column chunks
+    tl, k1, k2 = T // world, d // world, f // world
+    fs = layers.FsdpFFN(bf(w1[rank * k1:(rank + 1) * k1].contiguous()), bf(b1), bf(w2[rank * k2:(rank + 1) * k2].contiguous()),
+                        bf(b2), "gelu_tanh", tl, dist.group.WORLD, chunks=4)
+    for it in range(2):
+        y = fs.forward(bf(x[rank * tl:(rank + 1) * tl].contiguous()))
+    torch.cuda.synchronize()
+    err = (y.cpu().float() - want[rank * tl:(rank + 1) * tl]).abs()
+    good = bool((err <= 2e-2 * want[rank * tl:(rank + 1) * tl].abs() + 2e-2).all())
+    print(f"[rank {rank}] FSDP: max_abs={err.max().item():.3e} {'OK' if good else 'FAIL'}", flush=True)
+    ok &= good
+    # the generic host layer on a real 1 x world mesh: nn.ffn with NCCL collectives
+    P = ljs.PartitionSpec
+    mesh = ljs.Mesh(ljs.create_device_mesh((1, world)), ("data", "model"))
+    ns = lambda s: ljs.NamedSharding(mesh, s)
+    y = ljs.nn.ffn(ljs.device_put(x.reshape(4, T // 4, d), ns(P("data"))), ljs.device_put(w1, ns(P(None, "model"))),
+                   ljs.device_put(b1, ns(P("model"))), ljs.device_put(w2, ns(P("model", None))), ljs.device_put(b2, ns(P())),
+                   scatter_dim=1)
+    torch.cuda.synchronize()
+    blk = T // 4 // world
+    got = y.device_buffers[0].cpu().float()
+    ref = want.reshape(4, T // 4, d)[:, rank * blk:(rank + 1) * blk]
+    good = bool(((got - ref).abs() <= 2e-2 * ref.abs() + 2e-2).all())
+    print(f"[rank {rank}] nn.ffn (NamedSharding, NCCL reduce-scatter): {'OK' if good else 'FAIL'}", flush=True)
+    ok &= good
+    t = torch.tensor([1 if ok else 0], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    if rank == 0:
+        print("RESULT", "PASS" if t.item() == 1 else "FAIL", flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+    sys.exit(0 if t.item() == 1 else 1)
+
+
+if __name__ == "__main__":
+    main()
