@@ -109,7 +109,7 @@ def set_gemm_tuning(cta_group: int = 0, block_n: int = 0):
     _check(load().b200_gemm_set_tuning(cta_group, block_n), "b200_gemm_set_tuning")
 
 
-def set_gemm_group_m(group_m: int = 8):
+def set_gemm_group_m(group_m: int = 0):
     """Tile rasterisation group size (row-blocks that sweep the columns together). Tuning hook."""
     _check(load().b200_gemm_set_group_m(group_m), "b200_gemm_set_group_m")
 

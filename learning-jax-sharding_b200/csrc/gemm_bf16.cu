@@ -316,7 +316,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 // ------------------------------------------------------------------ host side
 static int g_force_cta_group = 0;   // 0 = heuristic; 1 / 2 force (set through b200_gemm_set_tuning)
 static int g_force_bn = 0;
-static int g_group_m = 8;
+static int g_group_m = 0;   // 0 = heuristic below
 
 template <int BN, int G, bool kBKmajor>
 static int launch_gemm(const void* A, int64_t lda, const void* B, int64_t ldb, const GemmParams& p0,
@@ -325,7 +325,15 @@ static int launch_gemm(const void* A, int64_t lda, const void* B, int64_t ldb, c
   GemmParams p = p0;
   p.tiles_m = (p.M + kBM * G - 1) / (kBM * G);
   p.tiles_n = (p.N + BN - 1) / BN;
-  p.group_m = g_group_m;
+  if (g_group_m > 0) {
+    p.group_m = g_group_m;
+  } else {
+    // keep the A panels of one group (group_m row-blocks x K) resident in L2 (~128 MB budget) while the
+    // B panels stream past: measured best 32 at K = 4096, 16 at K = 16384 (profiles/r01_gemm_raster_sweep.log)
+    const int64_t panel_bytes = static_cast<int64_t>(kBM) * G * p.K * 2;
+    int64_t gm = (128ll << 20) / (panel_bytes > 0 ? panel_bytes : 1);
+    p.group_m = static_cast<int>(gm < 4 ? 4 : (gm > 32 ? 32 : gm));
+  }
   CUtensorMap tmA, tmB;
   {
     uint64_t a_rows = static_cast<uint64_t>(p.M);
@@ -395,7 +403,7 @@ extern "C" int b200_gemm_set_tuning(int cta_group, int block_n) {
 }
 
 extern "C" int b200_gemm_set_group_m(int group_m) {
-  if (group_m < 1 || group_m > 1024) return fail(B200_ERR_INVALID_ARGUMENT, "group_m must be in [1, 1024]");
+  if (group_m < 0 || group_m > 1024) return fail(B200_ERR_INVALID_ARGUMENT, "group_m must be in [0, 1024]");
   g_group_m = group_m;
   return B200_OK;
 }
