@@ -88,6 +88,37 @@ int b200_gemm_bf16_rowblocked(const void* A, int64_t lda, int a_rows_per_block, 
                               int N, int K, int epilogue, void* stream);
 
 /*
+ * General form of b200_gemm_bf16.  Zero-initialise the struct, fill what you need.
+ * Besides the plain operands and the row-blocked A view it offers a ROW-BLOCK SCATTER of the
+ * output, the compute half of a fused "GEMM -> reduce-scatter" for row-parallel layers (the
+ * all-reduce XLA inserts after a contraction-sharded dot, case1a.py:49; the FFN's second Dense,
+ * case6_attention.py:36-40): with m_rows_per_block = R (a multiple of 256 dividing M), logical
+ * row m belongs to row block (m / R + m_block_rot) % (M / R); A is read from that block's rows and
+ * the bf16 result is written to c_block_ptrs[block] + (m % R) * ldc, where c_block_ptrs is a
+ * DEVICE array of M / R base pointers -- typically peer GPUs' receive slots mapped through CUDA
+ * IPC (b200_peer_*), so partial sums cross NVLink straight out of the GEMM epilogue, tile by
+ * tile, in 128-byte row segments.  m_block_rot staggers the ranks (rank r starts with block r+1)
+ * so that no two ranks push to the same destination at once.  c_block_ptrs = NULL keeps the
+ * result in C (rotation only).
+ */
+typedef struct {
+  const void* A;
+  int64_t lda;
+  int a_rows_per_block, a_block_stride; /* row-blocked A view, 0 = off (see b200_gemm_bf16_rowblocked) */
+  const void* B;
+  int64_t ldb;
+  int b_layout;
+  const void* bias;
+  void* C;
+  int64_t ldc;
+  int out_dtype;
+  void* const* c_block_ptrs;            /* device array of row-block base pointers, or NULL */
+  int m_rows_per_block, m_block_rot;    /* 0 = off */
+  int M, N, K, epilogue;
+} b200_gemm_args;
+int b200_gemm_bf16_ex(const b200_gemm_args* args, void* stream);
+
+/*
  * Batched true-fp32 GEMM (FFMA, no TF32): for b in [0,batch):
  *   C_b[M,N] = A_b[M,K] . B_b[K,N], all row-major, element strides lda/ldb/ldc
  *   between rows and strideA/strideB/strideC between batch items.
@@ -164,6 +195,31 @@ int b200_cast_bf16_to_f32(const void* src, float* dst, int64_t n, void* stream);
  * Finishes a row-parallel reduction whose partials were exchanged in f32. */
 int b200_sum_partials_to_bf16(const float* src, int64_t src_stride, int nsrc, const void* bias, int64_t cols,
                               void* dst, int64_t n, void* stream);
+
+/*
+ * Peer-memory plumbing of the fused GEMM -> reduce-scatter (one process per GPU on one NVSwitch box).
+ * SET-UP calls (they allocate / map device memory; not for the hot path):
+ *   b200_peer_alloc   cudaMalloc + zero-fill a receive buffer and return its 64-byte CUDA IPC handle;
+ *   b200_peer_open    map another rank's buffer from its handle (exchanged by the host layer, e.g.
+ *                     torch.distributed.all_gather); b200_peer_close / b200_peer_free undo them.
+ * HOT-PATH calls (enqueue only):
+ *   b200_peer_barrier every rank writes `epoch` into slot [rank] of each rank's flag block
+ *                     (flag_ptrs_dev: DEVICE array of `world` pointers to uint32[world] blocks, one per
+ *                     rank, inside the shared buffers) and waits until its own block shows >= epoch from
+ *                     everybody; epochs must increase by one per call.  All of this GPU's earlier peer
+ *                     stores on the stream are visible to the peers that pass the barrier.
+ *   b200_sum_bf16_partials  dst[i] = bf16(sum_r src[r*src_stride + i]) (+ bf16 bias[i % cols]), bf16 in,
+ *                     f32 accumulation: the local half of the reduce-scatter.
+ * No counterpart in the reference: XLA:CPU's in-process collectives between virtual devices play
+ * this role there.
+ */
+int b200_peer_alloc(uint64_t bytes, void** dev_ptr, void* handle64);
+int b200_peer_open(const void* handle64, void** dev_ptr);
+int b200_peer_close(void* dev_ptr);
+int b200_peer_free(void* dev_ptr);
+int b200_peer_barrier(void* const* flag_ptrs_dev, int rank, int world, uint32_t epoch, void* stream);
+int b200_sum_bf16_partials(const void* src, int64_t src_stride, int nsrc, const void* bias, int64_t cols, void* dst,
+                           int64_t n, void* stream);
 
 #ifdef __cplusplus
 }

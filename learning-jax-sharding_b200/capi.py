@@ -29,13 +29,30 @@ EXPORTED_SYMBOLS = (
     "b200_launch_count",
     "b200_gemm_bf16",
     "b200_gemm_bf16_rowblocked",
+    "b200_gemm_bf16_ex",
     "b200_gemm_f32",
     "b200_attention_fwd",
     "b200_ffn_fwd",
     "b200_cast_f32_to_bf16",
     "b200_cast_bf16_to_f32",
     "b200_sum_partials_to_bf16",
+    "b200_peer_alloc",
+    "b200_peer_open",
+    "b200_peer_close",
+    "b200_peer_free",
+    "b200_peer_barrier",
+    "b200_sum_bf16_partials",
 )
+
+
+class GemmArgs(ctypes.Structure):
+    """b200_gemm_args of include/b200_sharded.h."""
+    _fields_ = [("A", ctypes.c_void_p), ("lda", ctypes.c_int64), ("a_rows_per_block", ctypes.c_int),
+                ("a_block_stride", ctypes.c_int), ("B", ctypes.c_void_p), ("ldb", ctypes.c_int64),
+                ("b_layout", ctypes.c_int), ("bias", ctypes.c_void_p), ("C", ctypes.c_void_p), ("ldc", ctypes.c_int64),
+                ("out_dtype", ctypes.c_int), ("c_block_ptrs", ctypes.c_void_p), ("m_rows_per_block", ctypes.c_int),
+                ("m_block_rot", ctypes.c_int), ("M", ctypes.c_int), ("N", ctypes.c_int), ("K", ctypes.c_int),
+                ("epilogue", ctypes.c_int)]
 
 
 class B200Error(RuntimeError):
@@ -62,6 +79,13 @@ def load():
     lib.b200_launch_count.restype = i64
     lib.b200_gemm_bf16.argtypes = [vp, i64, vp, i64, i32, vp, vp, i64, i32, i32, i32, i32, i32, vp]
     lib.b200_gemm_bf16_rowblocked.argtypes = [vp, i64, i32, i32, vp, i64, i32, vp, vp, i64, i32, i32, i32, i32, i32, vp]
+    lib.b200_gemm_bf16_ex.argtypes = [ctypes.POINTER(GemmArgs), vp]
+    lib.b200_peer_alloc.argtypes = [ctypes.c_uint64, ctypes.POINTER(vp), vp]
+    lib.b200_peer_open.argtypes = [vp, ctypes.POINTER(vp)]
+    lib.b200_peer_close.argtypes = [vp]
+    lib.b200_peer_free.argtypes = [vp]
+    lib.b200_peer_barrier.argtypes = [vp, i32, i32, ctypes.c_uint32, vp]
+    lib.b200_sum_bf16_partials.argtypes = [vp, i64, i32, vp, i64, vp, i64, vp]
     lib.b200_gemm_f32.argtypes = [vp, i64, i64, vp, i64, i64, vp, i64, i64, i32, i32, i32, i32, i32, vp]
     lib.b200_attention_fwd.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32] + [i64] * 12 + [f32, i32, vp]
     lib.b200_ffn_fwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp]
@@ -262,4 +286,54 @@ def sum_partials_to_bf16(partials, bias=None, out=None):
         rc = load().b200_sum_partials_to_bf16(
             _ptr(partials), rows * cols, R, _ptr(bias), cols, _ptr(out), rows * cols, _stream(partials))
     _check(rc, "b200_sum_partials_to_bf16")
+    return out
+
+
+# ---------------------------------------------------------------- fused GEMM -> reduce-scatter plumbing
+def gemm_bf16_scatter(a, b, block_ptrs, rows_per_block: int, rot: int, ldc: int, *, b_layout=B_KN):
+    """a[M,K] @ b -> bf16 rows scattered to ``block_ptrs`` (a CUDA int64 tensor of M/rows_per_block base
+    pointers, e.g. peer GPUs' receive slots): b200_gemm_bf16_ex with the row-block scatter."""
+    _require_cuda(a, b, block_ptrs)
+    M, K = a.shape
+    N = b.shape[1] if b_layout == B_KN else b.shape[0]
+    args = GemmArgs()
+    args.A, args.lda = a.data_ptr(), a.stride(0)
+    args.B, args.ldb, args.b_layout = b.data_ptr(), b.stride(0), b_layout
+    args.C, args.ldc, args.out_dtype = None, ldc, BF16
+    args.c_block_ptrs = block_ptrs.data_ptr()
+    args.m_rows_per_block, args.m_block_rot = rows_per_block, rot
+    args.M, args.N, args.K, args.epilogue = M, N, K, EPI_NONE
+    with torch.cuda.device(a.device):
+        rc = load().b200_gemm_bf16_ex(ctypes.byref(args), _stream(a))
+    _check(rc, "b200_gemm_bf16_ex")
+
+
+def peer_alloc(nbytes: int):
+    """(device pointer, 64-byte IPC handle) of a zero-filled buffer other ranks can map. Set-up only."""
+    ptr = ctypes.c_void_p()
+    handle = ctypes.create_string_buffer(64)
+    _check(load().b200_peer_alloc(nbytes, ctypes.byref(ptr), handle), "b200_peer_alloc")
+    return int(ptr.value), handle.raw
+
+
+def peer_open(handle: bytes) -> int:
+    ptr = ctypes.c_void_p()
+    buf = ctypes.create_string_buffer(handle, 64)
+    _check(load().b200_peer_open(buf, ctypes.byref(ptr)), "b200_peer_open")
+    return int(ptr.value)
+
+
+def peer_barrier(flag_ptrs, rank: int, world: int, epoch: int):
+    with torch.cuda.device(flag_ptrs.device):
+        rc = load().b200_peer_barrier(_ptr(flag_ptrs), rank, world, epoch & 0xFFFFFFFF, _stream(flag_ptrs))
+    _check(rc, "b200_peer_barrier")
+
+
+def sum_bf16_partials(src_ptr: int, src_stride: int, nsrc: int, bias, cols: int, out):
+    """out[rows, cols] = bf16(sum_r partial_r) (+bias); partials are raw device memory at src_ptr."""
+    _require_cuda(bias, out)
+    with torch.cuda.device(out.device):
+        rc = load().b200_sum_bf16_partials(ctypes.c_void_p(src_ptr), src_stride, nsrc, _ptr(bias), cols, _ptr(out),
+                                           out.numel(), _stream(out))
+    _check(rc, "b200_sum_bf16_partials")
     return out

@@ -30,11 +30,12 @@ struct GemmCfg {
   static constexpr int kABytes = kBM * kBK * 2;                 // 16 KB
   static constexpr int kBBytes = kBNcta * kBK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kSmemBudget = 227 * 1024 - 1024 /*align slack*/ - 256 /*barriers*/;
+  static constexpr int kStoreStageBytes = 4 * 32 * 128;         // per epilogue warp: 32 rows x 128 B
+  static constexpr int kSmemBudget = 227 * 1024 - 1024 /*align slack*/ - 256 /*barriers*/ - kStoreStageBytes;
   static constexpr int kStages = kSmemBudget / kStageBytes > 8 ? 8 : kSmemBudget / kStageBytes;
   static constexpr int kAccStages = 2;
   static constexpr int kTmemCols = 512;
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kStoreStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
 struct GemmParams {
@@ -49,6 +50,11 @@ struct GemmParams {
   // (m / a_rows_per_block) * a_block_stride + m % a_rows_per_block   (0 = plain row-major)
   int a_rows_per_block, a_block_stride;
   int group_m;   // tile rasterisation: group_m row-blocks sweep all column-blocks together (L2 reuse)
+  // optional row-block scatter of the OUTPUT (fused reduce-scatter push): logical row m belongs to row block
+  // (m / m_rows_per_block + m_block_rot) % m_num_blocks; A is read from that physical block and C is written
+  // to c_block_ptrs[block] (a peer GPU's receive slot, or local memory) at row m % m_rows_per_block.
+  void* const* c_block_ptrs;
+  int m_rows_per_block, m_block_rot, m_num_blocks;
 };
 
 __device__ __forceinline__ float gelu_tanh_f(float x) {
@@ -86,7 +92,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   using Cfg = GemmCfg<BN, G>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+  uint8_t* store_stage = smem + Cfg::kStages * Cfg::kStageBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(store_stage + Cfg::kStoreStageBytes);
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + Cfg::kStages;
   uint64_t* tmem_full_bar = bars + 2 * Cfg::kStages;
@@ -140,6 +147,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       int m_blk, n_blk;
       tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, m_blk, n_blk);
       int m0 = (m_blk * G + cta_rank) * kBM;
+      if (p.m_rows_per_block > 0)
+        m0 = ((m0 / p.m_rows_per_block + p.m_block_rot) % p.m_num_blocks) * p.m_rows_per_block +
+             m0 % p.m_rows_per_block;
       if (p.a_rows_per_block > 0) m0 = (m0 / p.a_rows_per_block) * p.a_block_stride + m0 % p.a_rows_per_block;
       const int n0 = n_blk * BN + cta_rank * Cfg::kBNcta;
       for (int kb = 0; kb < num_kb; ++kb) {
@@ -226,14 +236,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       mbar_wait(&tmem_full_bar[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+      if (out_f32) {
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32(taddr + c * 32, r);
-        tmem_wait_ld();
-        const int col0 = n0 + c * 32;
-        if (row < p.M && col0 < p.N) {
-          if (out_f32) {
+        for (int c = 0; c < BN / 32; ++c) {
+          uint32_t r[32];
+          tmem_ld_32x32(taddr + c * 32, r);
+          tmem_wait_ld();
+          const int col0 = n0 + c * 32;
+          if (row < p.M && col0 < p.N) {
             float* dst = reinterpret_cast<float*>(p.C) + static_cast<int64_t>(row) * p.ldc + col0;
 #pragma unroll
             for (int j = 0; j < 32; j += 4) {
@@ -253,38 +263,73 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 *reinterpret_cast<float4*>(dst + j) = v;
               }
             }
-          } else {
-            __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.C) + static_cast<int64_t>(row) * p.ldc + col0;
+          }
+        }
+      } else {
+        // bf16: 64 columns at a time through this warp's 4 KB staging tile (128-byte rows, 16-byte units
+        // XOR-swizzled by row), so every warp store instruction writes 4 rows x 128 contiguous bytes --
+        // full sectors in local HBM and full-size packets when the destination is a peer GPU.
+        const int row_base = (m_blk * G + cta_rank) * kBM + q * 32;       // logical row of lane 0
+        __nv_bfloat16* cbase;
+        if (p.m_rows_per_block > 0) {
+          const int blk = (row_base / p.m_rows_per_block + p.m_block_rot) % p.m_num_blocks;
+          const int local = row_base % p.m_rows_per_block;
+          cbase = p.c_block_ptrs != nullptr
+                      ? reinterpret_cast<__nv_bfloat16*>(p.c_block_ptrs[blk]) + static_cast<int64_t>(local) * p.ldc
+                      : reinterpret_cast<__nv_bfloat16*>(p.C) +
+                            (static_cast<int64_t>(blk) * p.m_rows_per_block + local) * p.ldc;
+        } else {
+          cbase = reinterpret_cast<__nv_bfloat16*>(p.C) + static_cast<int64_t>(row_base) * p.ldc;
+        }
+        uint8_t* stg = store_stage + q * (32 * 128);
+#pragma unroll 1
+        for (int c2 = 0; c2 < BN / 64; ++c2) {
+          const int col0 = n0 + c2 * 64;
+#pragma unroll
+          for (int half = 0; half < 2; ++half) {
+            uint32_t r[32];
+            tmem_ld_32x32(taddr + c2 * 64 + half * 32, r);
+            tmem_wait_ld();
 #pragma unroll
             for (int j = 0; j < 32; j += 8) {
-              if (col0 + j < p.N) {     // N % 8 == 0: a group of 8 columns is all in or all out
-                float bv[8];
-                if (has_bias) {
-                  uint4 braw = *reinterpret_cast<const uint4*>(p.bias + col0 + j);
-                  const __nv_bfloat162* b2 = reinterpret_cast<const __nv_bfloat162*>(&braw);
+              const int col = col0 + half * 32 + j;
+              float bv[8];
 #pragma unroll
-                  for (int t = 0; t < 4; ++t) {
-                    float2 f = __bfloat1622float2(b2[t]);
-                    bv[2 * t] = f.x;
-                    bv[2 * t + 1] = f.y;
-                  }
-                } else {
+              for (int t = 0; t < 8; ++t) bv[t] = 0.f;
+              if (has_bias && col < p.N) {      // N % 8 == 0: a group of 8 columns is all in or all out
+                uint4 braw = *reinterpret_cast<const uint4*>(p.bias + col);
+                const __nv_bfloat162* b2 = reinterpret_cast<const __nv_bfloat162*>(&braw);
 #pragma unroll
-                  for (int t = 0; t < 8; ++t) bv[t] = 0.f;
+                for (int t = 0; t < 4; ++t) {
+                  float2 f = __bfloat1622float2(b2[t]);
+                  bv[2 * t] = f.x;
+                  bv[2 * t + 1] = f.y;
                 }
-                uint4 o;
-                o.x = pack_bf16x2(apply_epilogue(__uint_as_float(r[j + 0]), bv[0], p.epilogue, false),
-                                  apply_epilogue(__uint_as_float(r[j + 1]), bv[1], p.epilogue, false));
-                o.y = pack_bf16x2(apply_epilogue(__uint_as_float(r[j + 2]), bv[2], p.epilogue, false),
-                                  apply_epilogue(__uint_as_float(r[j + 3]), bv[3], p.epilogue, false));
-                o.z = pack_bf16x2(apply_epilogue(__uint_as_float(r[j + 4]), bv[4], p.epilogue, false),
-                                  apply_epilogue(__uint_as_float(r[j + 5]), bv[5], p.epilogue, false));
-                o.w = pack_bf16x2(apply_epilogue(__uint_as_float(r[j + 6]), bv[6], p.epilogue, false),
-                                  apply_epilogue(__uint_as_float(r[j + 7]), bv[7], p.epilogue, false));
-                *reinterpret_cast<uint4*>(dst + j) = o;
               }
+              uint4 o;
+              o.x = pack_bf16x2(apply_epilogue(__uint_as_float(r[j + 0]), bv[0], p.epilogue, false),
+                                apply_epilogue(__uint_as_float(r[j + 1]), bv[1], p.epilogue, false));
+              o.y = pack_bf16x2(apply_epilogue(__uint_as_float(r[j + 2]), bv[2], p.epilogue, false),
+                                apply_epilogue(__uint_as_float(r[j + 3]), bv[3], p.epilogue, false));
+              o.z = pack_bf16x2(apply_epilogue(__uint_as_float(r[j + 4]), bv[4], p.epilogue, false),
+                                apply_epilogue(__uint_as_float(r[j + 5]), bv[5], p.epilogue, false));
+              o.w = pack_bf16x2(apply_epilogue(__uint_as_float(r[j + 6]), bv[6], p.epilogue, false),
+                                apply_epilogue(__uint_as_float(r[j + 7]), bv[7], p.epilogue, false));
+              const int unit = half * 4 + (j >> 3);
+              *reinterpret_cast<uint4*>(stg + lane * 128 + ((unit ^ (lane & 7)) << 4)) = o;
             }
           }
+          __syncwarp();
+#pragma unroll
+          for (int it = 0; it < 8; ++it) {
+            const int rr = it * 4 + (lane >> 3);
+            const int unit = lane & 7;
+            const uint4 v = *reinterpret_cast<const uint4*>(stg + rr * 128 + ((unit ^ (rr & 7)) << 4));
+            const int gcol = col0 + unit * 8;
+            if (row_base + rr < p.M && gcol < p.N)
+              *reinterpret_cast<uint4*>(cbase + static_cast<int64_t>(rr) * p.ldc + gcol) = v;
+          }
+          __syncwarp();
         }
       }
       // accumulator stage drained: hand it back to the MMA issuer (in the leader CTA)
@@ -411,18 +456,47 @@ extern "C" int b200_gemm_set_group_m(int group_m) {
 extern "C" int b200_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, int b_layout,
                               const void* bias, void* C, int64_t ldc, int out_dtype, int M, int N, int K,
                               int epilogue, void* stream) {
-  return b200_gemm_bf16_rowblocked(A, lda, 0, 0, B, ldb, b_layout, bias, C, ldc, out_dtype, M, N, K, epilogue,
-                                   stream);
+  b200_gemm_args a = {};
+  a.A = A; a.lda = lda; a.B = B; a.ldb = ldb; a.b_layout = b_layout; a.bias = bias; a.C = C; a.ldc = ldc;
+  a.out_dtype = out_dtype; a.M = M; a.N = N; a.K = K; a.epilogue = epilogue;
+  return b200_gemm_bf16_ex(&a, stream);
 }
 
 extern "C" int b200_gemm_bf16_rowblocked(const void* A, int64_t lda, int a_rows_per_block, int a_block_stride,
                                          const void* B, int64_t ldb, int b_layout, const void* bias, void* C,
                                          int64_t ldc, int out_dtype, int M, int N, int K, int epilogue,
                                          void* stream) {
-  B200_REQUIRE(A && B && C, "b200_gemm_bf16: null operand pointer");
+  b200_gemm_args a = {};
+  a.A = A; a.lda = lda; a.a_rows_per_block = a_rows_per_block; a.a_block_stride = a_block_stride;
+  a.B = B; a.ldb = ldb; a.b_layout = b_layout; a.bias = bias; a.C = C; a.ldc = ldc;
+  a.out_dtype = out_dtype; a.M = M; a.N = N; a.K = K; a.epilogue = epilogue;
+  return b200_gemm_bf16_ex(&a, stream);
+}
+
+extern "C" int b200_gemm_bf16_ex(const b200_gemm_args* args, void* stream) {
+  B200_REQUIRE(args != nullptr, "b200_gemm_bf16: null argument block");
+  const void* A = args->A;
+  const void* B = args->B;
+  const void* bias = args->bias;
+  void* C = args->C;
+  const int64_t lda = args->lda, ldb = args->ldb, ldc = args->ldc;
+  const int b_layout = args->b_layout, out_dtype = args->out_dtype, epilogue = args->epilogue;
+  const int M = args->M, N = args->N, K = args->K;
+  const int a_rows_per_block = args->a_rows_per_block, a_block_stride = args->a_block_stride;
+  const bool scatter = args->c_block_ptrs != nullptr;
+  B200_REQUIRE(A && B && (C || scatter), "b200_gemm_bf16: null operand pointer");
   B200_REQUIRE(a_rows_per_block >= 0 && a_block_stride >= 0, "b200_gemm_bf16: negative row-block parameters");
   B200_REQUIRE(a_rows_per_block == 0 || (a_rows_per_block % 128 == 0 && a_block_stride >= a_rows_per_block),
                "b200_gemm_bf16: a_rows_per_block must be a multiple of 128 and <= a_block_stride");
+  B200_REQUIRE(args->m_rows_per_block >= 0 && args->m_block_rot >= 0, "b200_gemm_bf16: negative m-block parameters");
+  if (args->m_rows_per_block > 0) {
+    B200_REQUIRE(args->m_rows_per_block % 256 == 0 && M % args->m_rows_per_block == 0,
+                 "b200_gemm_bf16: m_rows_per_block must be a multiple of 256 that divides M");
+    B200_REQUIRE(out_dtype == B200_BF16, "b200_gemm_bf16: row-block scatter writes bf16 only");
+    B200_REQUIRE(a_rows_per_block == 0, "b200_gemm_bf16: row-block scatter and the row-blocked A view exclude each other");
+  } else {
+    B200_REQUIRE(!scatter, "b200_gemm_bf16: c_block_ptrs needs m_rows_per_block");
+  }
   B200_REQUIRE(M > 0 && N > 0 && K > 0, "b200_gemm_bf16: M, N, K must be positive (got %d, %d, %d)", M, N, K);
   B200_REQUIRE(K % 8 == 0 && N % 8 == 0, "b200_gemm_bf16: K and N must be multiples of 8 (got K=%d N=%d)", K, N);
   B200_REQUIRE(b_layout == B200_B_KN || b_layout == B200_B_NK, "b200_gemm_bf16: bad b_layout %d", b_layout);
@@ -450,6 +524,10 @@ extern "C" int b200_gemm_bf16_rowblocked(const void* A, int64_t lda, int a_rows_
   p.out_f32 = out_dtype == B200_F32;
   p.a_rows_per_block = a_rows_per_block;
   p.a_block_stride = a_block_stride;
+  p.c_block_ptrs = args->c_block_ptrs;
+  p.m_rows_per_block = args->m_rows_per_block;
+  p.m_block_rot = args->m_block_rot;
+  p.m_num_blocks = args->m_rows_per_block > 0 ? M / args->m_rows_per_block : 0;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const bool kmajor = b_layout == B200_B_NK;
 

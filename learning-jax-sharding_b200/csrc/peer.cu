@@ -1,0 +1,148 @@
+// Peer-memory plumbing for the fused "GEMM -> reduce-scatter" of row-parallel layers (one process per
+// GPU, NVLink 5 / NVSwitch): receive buffers shared through CUDA IPC, a cross-GPU barrier on flags in
+// those buffers, and the local reduction of the received bf16 partials.
+//
+// Step of a row-parallel layer on rank r (W ranks, T rows, R = T / W rows per owner):
+//   1. b200_gemm_bf16_ex with c_block_ptrs[p] = rank p's receive slot [r]: every finished tile of the
+//      partial product is stored straight into its owner's memory from the GEMM epilogue;
+//   2. b200_peer_barrier: all ranks' pushes are complete and visible;
+//   3. b200_sum_bf16_partials: y[R, N] = bf16( sum_s recv[s][R, N] ) (+ bias), f32 accumulation.
+// This replaces the all-reduce / reduce-scatter XLA inserts after a contraction-sharded dot
+// (reference pattern: case1a.py:24-49; FFN second Dense, case6_attention.py:36-40).
+#include <string.h>
+
+#include "host_common.h"
+#include "sm100_ptx.cuh"
+
+namespace b200 {
+
+__global__ void peer_barrier_kernel(uint32_t* const* flag_ptrs, int rank, int world, uint32_t epoch) {
+  // thread p signals rank p, then waits for rank p's signal in this rank's own flag block
+  const int peer = threadIdx.x;
+  if (peer >= world) return;
+  __threadfence_system();   // this GPU's earlier peer stores (previous kernels in the stream) are ordered before the flag
+  uint32_t* remote = flag_ptrs[peer] + rank;
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(remote), "r"(epoch) : "memory");
+  const uint32_t* mine = flag_ptrs[rank] + peer;
+  const long long t0 = clock64();
+  uint32_t seen;
+  do {
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(mine) : "memory");
+    if (clock64() - t0 > 4000000000ll) {   // ~2 s: a rank is missing -- fail instead of hanging the GPU
+      printf("b200: peer barrier timeout rank=%d waiting for rank %d epoch=%u seen=%u\n", rank, peer, epoch, seen);
+      __trap();
+    }
+  } while (static_cast<int32_t>(seen - epoch) < 0);
+}
+
+// dst[i] = bf16(sum_r src[r*stride + i]) (+ bias[i % cols]); 8 elements per thread, f32 accumulation
+__global__ void __launch_bounds__(256) sum_bf16_partials_kernel(const __nv_bfloat16* __restrict__ src,
+                                                               int64_t src_stride, int nsrc,
+                                                               const __nv_bfloat16* __restrict__ bias, int64_t cols,
+                                                               __nv_bfloat16* __restrict__ dst, int64_t n) {
+  const int64_t nvec = n / 8;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+    float acc[8];
+#pragma unroll
+    for (int t = 0; t < 8; ++t) acc[t] = 0.f;
+    for (int r = 0; r < nsrc; ++r) {
+      const uint4 v = reinterpret_cast<const uint4*>(src + r * src_stride)[i];
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const float2 f = __bfloat1622float2(h[t]);
+        acc[2 * t] += f.x;
+        acc[2 * t + 1] += f.y;
+      }
+    }
+    if (bias != nullptr) {   // Dense semantics: round the sum to bf16, then add the bf16 bias in bf16
+      const uint4 bv = *reinterpret_cast<const uint4*>(bias + (i * 8) % cols);
+      const __nv_bfloat162* hb = reinterpret_cast<const __nv_bfloat162*>(&bv);
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const float2 f = __bfloat1622float2(hb[t]);
+        acc[2 * t] = bf16_round(acc[2 * t]) + f.x;
+        acc[2 * t + 1] = bf16_round(acc[2 * t + 1]) + f.y;
+      }
+    }
+    uint4 o;
+    o.x = pack_bf16x2(acc[0], acc[1]);
+    o.y = pack_bf16x2(acc[2], acc[3]);
+    o.z = pack_bf16x2(acc[4], acc[5]);
+    o.w = pack_bf16x2(acc[6], acc[7]);
+    reinterpret_cast<uint4*>(dst)[i] = o;
+  }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_peer_alloc(uint64_t bytes, void** dev_ptr, void* handle64) {
+  B200_REQUIRE(bytes > 0 && dev_ptr && handle64, "b200_peer_alloc: bad arguments");
+  void* p = nullptr;
+  B200_CUDA_CHECK(cudaMalloc(&p, bytes));
+  cudaError_t e = cudaMemset(p, 0, bytes);
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  cudaIpcMemHandle_t h;
+  if (e == cudaSuccess) e = cudaIpcGetMemHandle(&h, p);
+  if (e != cudaSuccess) {
+    cudaFree(p);
+    return fail(B200_ERR_CUDA, "b200_peer_alloc: %s", cudaGetErrorString(e));
+  }
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle is 64 bytes");
+  memcpy(handle64, &h, 64);
+  *dev_ptr = p;
+  return B200_OK;
+}
+
+extern "C" int b200_peer_open(const void* handle64, void** dev_ptr) {
+  B200_REQUIRE(handle64 && dev_ptr, "b200_peer_open: bad arguments");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  void* p = nullptr;
+  B200_CUDA_CHECK(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+  *dev_ptr = p;
+  return B200_OK;
+}
+
+extern "C" int b200_peer_close(void* dev_ptr) {
+  B200_CUDA_CHECK(cudaIpcCloseMemHandle(dev_ptr));
+  return B200_OK;
+}
+
+extern "C" int b200_peer_free(void* dev_ptr) {
+  B200_CUDA_CHECK(cudaFree(dev_ptr));
+  return B200_OK;
+}
+
+extern "C" int b200_peer_barrier(void* const* flag_ptrs_dev, int rank, int world, uint32_t epoch, void* stream) {
+  B200_REQUIRE(flag_ptrs_dev && world >= 1 && world <= 64 && rank >= 0 && rank < world,
+               "b200_peer_barrier: bad arguments (world must be 1..64)");
+  peer_barrier_kernel<<<1, 64, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<uint32_t* const*>(flag_ptrs_dev), rank, world, epoch);
+  B200_CUDA_CHECK(cudaGetLastError());
+  launch_counter().fetch_add(1);
+  return B200_OK;
+}
+
+extern "C" int b200_sum_bf16_partials(const void* src, int64_t src_stride, int nsrc, const void* bias, int64_t cols,
+                                      void* dst, int64_t n, void* stream) {
+  B200_REQUIRE(src && dst && nsrc >= 1 && n >= 0, "b200_sum_bf16_partials: bad arguments");
+  B200_REQUIRE(n % 8 == 0 && src_stride % 8 == 0, "b200_sum_bf16_partials: n and src_stride must be multiples of 8");
+  B200_REQUIRE(!bias || (cols > 0 && cols % 8 == 0 && n % cols == 0),
+               "b200_sum_bf16_partials: cols must be a positive multiple of 8 dividing n when bias is given");
+  B200_REQUIRE((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(bias)) % 16 == 0,
+               "b200_sum_bf16_partials: buffers must be 16-byte aligned");
+  if (n == 0) return B200_OK;
+  const int sms = num_sms();
+  int64_t blocks = (n / 8 + 255) / 256;
+  if (blocks > static_cast<int64_t>(sms) * 8) blocks = static_cast<int64_t>(sms) * 8;
+  sum_bf16_partials_kernel<<<static_cast<int>(blocks), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const __nv_bfloat16*>(src), src_stride, nsrc, reinterpret_cast<const __nv_bfloat16*>(bias),
+      cols > 0 ? cols : 8, reinterpret_cast<__nv_bfloat16*>(dst), n);
+  B200_CUDA_CHECK(cudaGetLastError());
+  launch_counter().fetch_add(1);
+  return B200_OK;
+}

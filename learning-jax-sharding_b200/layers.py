@@ -13,6 +13,7 @@ from __future__ import annotations
 
 import json
 import os
+import sys
 from typing import Optional
 
 import torch
@@ -103,6 +104,67 @@ class TensorParallelFFN:
                 self.comm_stream.wait_event(self.chunk_done[c])
                 self.dist.reduce_scatter_tensor(self.y[c * rows_blk:(c + 1) * rows_blk], yc, group=self.group)
         main.wait_stream(self.comm_stream)
+        return self.y
+
+
+class FusedTensorParallelFFN:
+    """Tensor-parallel FFN whose row-parallel reduction is fused into the second GEMM: every finished tile
+    of the partial y is stored from the GEMM epilogue straight into its owner's receive slot over NVLink
+    (CUDA-IPC-mapped peer memory), ranks staggered so each destination has one sender at a time; then a
+    flag barrier and one local pass summing the W received bf16 partials in f32 (+ b2).  No NCCL on the
+    data path, no token chunking (both GEMMs run at full size).  Same result layout as
+    TensorParallelFFN: this rank's sequence block y[rank*T/W : (rank+1)*T/W]."""
+
+    _FLAG_BYTES = 1024
+
+    def __init__(self, w1, b1, w2, b2, act: str, T: int, group):
+        import torch.distributed as dist
+        self.dist, self.group = dist, group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.w1, self.b1, self.w2, self.b2 = w1, b1, w2, b2
+        self.act = _act_code(act, b1 is not None)
+        self.d_model, self.F = w1.shape
+        self.T = T
+        W = self.world
+        if T % W or (T // W) % 256:
+            raise ValueError(f"T={T} must split into {W} blocks of a multiple of 256 rows")
+        self.R = T // W
+        dev = w1.device
+        self.slot = self.R * self.d_model                      # elements of one receive slot
+        total = self._FLAG_BYTES + 2 * W * self.slot * 2       # flags + two receive buffers of W slots
+        self.base, handle = capi.peer_alloc(total)
+        mine = torch.tensor(list(handle), dtype=torch.uint8, device=dev)
+        handles = [torch.empty_like(mine) for _ in range(W)]
+        dist.all_gather(handles, mine, group=group)
+        self.peer_base = []
+        for p in range(W):
+            self.peer_base.append(self.base if p == self.rank else capi.peer_open(bytes(handles[p].cpu().tolist())))
+        self.flag_ptrs = torch.tensor(self.peer_base, dtype=torch.int64, device=dev)
+        self.c_ptrs = []
+        for buf in range(2):
+            ptrs = [self.peer_base[p] + self._FLAG_BYTES + ((buf * W + self.rank) * self.slot) * 2 for p in range(W)]
+            self.c_ptrs.append(torch.tensor(ptrs, dtype=torch.int64, device=dev))
+        self.h = torch.empty((T, self.F), dtype=torch.bfloat16, device=dev)
+        self.y = torch.empty((self.R, self.d_model), dtype=torch.bfloat16, device=dev)
+        self.buf = 0
+        self.epoch = 0
+        dist.barrier(group=group)
+
+    def forward(self, x: torch.Tensor, record=None) -> torch.Tensor:
+        W = self.world
+        if record is not None:
+            record("start")
+        capi.gemm_bf16(x, self.w1, bias=self.b1, epilogue=self.act, out=self.h)
+        if record is not None:
+            record("gemm1")
+        capi.gemm_bf16_scatter(self.h, self.w2, self.c_ptrs[self.buf], self.R, (self.rank + 1) % W, self.d_model)
+        if record is not None:
+            record("gemm2")
+        self.epoch += 1
+        capi.peer_barrier(self.flag_ptrs, self.rank, W, self.epoch)
+        src = self.base + self._FLAG_BYTES + (self.buf * W * self.slot) * 2
+        capi.sum_bf16_partials(src, self.slot, W, self.b2, self.d_model, self.y)
+        self.buf ^= 1
         return self.y
 
 
@@ -206,10 +268,23 @@ class FFNBench:
         else:
             fl = f // world
             self.x_host = x.pin_memory()
-            self.layer = TensorParallelFFN(w1[:, rank * fl:(rank + 1) * fl].contiguous().to(dev),
-                                           b1[rank * fl:(rank + 1) * fl].contiguous().to(dev),
-                                           w2[rank * fl:(rank + 1) * fl].contiguous().to(dev), b2.to(dev), act, T, group,
-                                           chunks=chunks)
+            shard = (w1[:, rank * fl:(rank + 1) * fl].contiguous().to(dev), b1[rank * fl:(rank + 1) * fl].contiguous().to(dev),
+                     w2[rank * fl:(rank + 1) * fl].contiguous().to(dev), b2.to(dev))
+            self.collective = "none"
+            if world > 1 and os.environ.get("B200_TP_COLLECTIVE", "fused") == "fused":
+                try:
+                    self.layer = FusedTensorParallelFFN(*shard, act, T, group)
+                    self.collective = "fused GEMM epilogue push over NVLink peer memory + local reduce"
+                except Exception as e:   # noqa: BLE001 - e.g. CUDA IPC not permitted in this container
+                    if rank == 0:
+                        print(f"[bench] fused reduce-scatter unavailable ({e!r}); using NCCL", file=sys.stderr, flush=True)
+                    self.layer = None
+            else:
+                self.layer = None
+            if self.layer is None:
+                self.layer = TensorParallelFFN(*shard, act, T, group, chunks=chunks)
+                if world > 1:
+                    self.collective = "NCCL reduce-scatter per token chunk on a side stream"
             self.T_in, self.T_out = T, T // world
         self.x = self.x_host.to(dev)
         self.y_host = torch.empty((self.T_out, d), dtype=torch.bfloat16).pin_memory()
@@ -224,7 +299,9 @@ class FFNBench:
     def parallelism_name(self):
         if self.mode == "single":
             return "1 GPU"
-        return f"{'tp' if self.mode == 'tp' else 'fsdp'}{self.world} (mesh {'1x%d' % self.world if self.mode == 'tp' else '%dx1' % self.world})"
+        mesh = "1x%d" % self.world if self.mode == "tp" else "%dx1" % self.world
+        coll = getattr(self, "collective", "NCCL all-gather of weight column chunks on a side stream")
+        return f"{'tp' if self.mode == 'tp' else 'fsdp'}{self.world} (mesh {mesh}; {coll})"
 
     # --- kernel-resident step
     def reset_kernel_events(self):

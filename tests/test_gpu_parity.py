@@ -295,3 +295,32 @@ def test_casts_and_partials(ljs):
     got = capi.sum_partials_to_bf16(_dev(parts), bias=_dev(bias)).cpu()
     want = ((parts.sum(0).to(torch.bfloat16).float() + bias.float())).to(torch.bfloat16)
     torch.testing.assert_close(got.float(), want.float(), rtol=1e-2, atol=1e-2)
+
+
+def test_gemm_row_block_scatter_and_partial_sum(ljs):
+    """b200_gemm_bf16_ex's row-block scatter (the compute half of the fused reduce-scatter) with the
+    'peer' slots being separate local buffers, and b200_sum_bf16_partials (the local half)."""
+    capi = ljs.capi
+    M, N, K, W = 1024, 512, 384, 4
+    R = M // W
+    a = rm.synthetic((M, K), 70).to(torch.bfloat16)
+    w = rm.synthetic((K, N), 71, "weight").to(torch.bfloat16)
+    want = rm.dense_bf16(a, w).float()
+    slots = [torch.zeros((R, N), dtype=torch.bfloat16, device="cuda") for _ in range(W)]
+    ptrs = torch.tensor([s.data_ptr() for s in slots], dtype=torch.int64, device="cuda")
+    for rot in (0, 1, 3):
+        for s in slots:
+            s.zero_()
+        capi.gemm_bf16_scatter(_dev(a), _dev(w), ptrs, R, rot, N)
+        torch.cuda.synchronize()
+        # physical block b (rows [bR, (b+1)R) of A) lands in slot b whatever the rotation
+        for b in range(W):
+            torch.testing.assert_close(slots[b].cpu().float(), want[b * R:(b + 1) * R], **BF16_TOL)
+    # local reduction of W bf16 partials (+ bias)
+    parts = rm.synthetic((W, R, N), 72).to(torch.bfloat16)
+    bias = rm.synthetic((N,), 73, "bias").to(torch.bfloat16)
+    pd = _dev(parts)
+    out = torch.empty((R, N), dtype=torch.bfloat16, device="cuda")
+    capi.sum_bf16_partials(pd.data_ptr(), R * N, W, _dev(bias), N, out)
+    ref = (parts.float().sum(0).to(torch.bfloat16).float() + bias.float()).to(torch.bfloat16)
+    torch.testing.assert_close(out.cpu().float(), ref.float(), rtol=1e-2, atol=1e-2)

@@ -41,6 +41,18 @@ def main():
         good = bool((err <= 2e-2 * want[rank * blk:(rank + 1) * blk].abs() + 2e-2).all())
         print(f"[rank {rank}] TP chunks={tp.chunks}: max_abs={err.max().item():.3e} {'OK' if good else 'FAIL'}", flush=True)
         ok &= good
+    # fused: GEMM2 epilogue pushes partial tiles into the owners' receive slots over NVLink peer memory
+    fused = layers.FusedTensorParallelFFN(bf(w1[:, rank * fl:(rank + 1) * fl].contiguous()), bf(b1[rank * fl:(rank + 1) * fl]),
+                                          bf(w2[rank * fl:(rank + 1) * fl].contiguous()), bf(b2), "gelu_tanh", T,
+                                          dist.group.WORLD)
+    for it in range(5):     # several steps: both receive buffers and the barrier epochs are exercised
+        y = fused.forward(bf(x))
+    torch.cuda.synchronize()
+    blk = T // world
+    err = (y.cpu().float() - want[rank * blk:(rank + 1) * blk]).abs()
+    good = bool((err <= 2e-2 * want[rank * blk:(rank + 1) * blk].abs() + 2e-2).all())
+    print(f"[rank {rank}] fused TP (peer-memory push): max_abs={err.max().item():.3e} {'OK' if good else 'FAIL'}", flush=True)
+    ok &= good
     # FSDP: tokens over ranks, weights dim0-sharded, all-gather in column chunks
     tl, k1, k2 = T // world, d // world, f // world
     fs = layers.FsdpFFN(bf(w1[rank * k1:(rank + 1) * k1].contiguous()), bf(b1), bf(w2[rank * k2:(rank + 1) * k2].contiguous()),
