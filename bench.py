@@ -197,6 +197,7 @@ def main():
     ap.add_argument("--workload", default="case4_gspmd_ff")
     ap.add_argument("--act", default="gelu_tanh", choices=["gelu_tanh", "relu"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-attention", action="store_true", help="skip the supplementary attention measurement")
     ap.add_argument("--chunks", type=int, default=4, help="token chunks for collective / copy overlap")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
@@ -309,6 +310,19 @@ def main():
                      "peak_source": peaks["source"], "launch_ms": kernel_ms, "flops_per_launch": flops_per_launch,
                      "traffic": bench.ncu_traffic_bytes()},
     }
+    if world == 1 and not args.no_attention:
+        # supplementary: the MHA layer of configs[3] (case5_attention_dense shape) on this GPU
+        del bench
+        torch.cuda.empty_cache()
+        acfg = ATTN_WORKLOADS["case5_attention_dense"]
+        r = layers.run_attention_workload(acfg, 0, 1, dev, steps=5, warmup=2)
+        tot = r["core_flops"] + r["proj_flops"]
+        line["attention"] = {
+            "workload": "case5_attention_dense (B8, S4096, 32 heads x 128, non-causal; q/k/v/out projections + core)",
+            "value": tot / (r["ms_per_step"] * 1e-3) / 1e12, "unit": UNIT, "ms_per_step": r["ms_per_step"],
+            "core_tflops": r["core_flops"] / (r["parts_ms"]["attn"] * 1e-3) / 1e12,
+            "core_frac_of_peak": r["core_flops"] / (r["parts_ms"]["attn"] * 1e-3) / 1e12 / peaks["bf16_burst"],
+            "parts_ms": r["parts_ms"], "gpu_launches": r["launches"]}
     if not args.no_cpu_baseline and world == 1:
         line["cpu_baseline"] = cpu_ffn_sample(cfg, act=args.act)
     else:

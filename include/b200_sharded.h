@@ -217,6 +217,12 @@ int b200_peer_alloc(uint64_t bytes, void** dev_ptr, void* handle64);
 int b200_peer_open(const void* handle64, void** dev_ptr);
 int b200_peer_close(void* dev_ptr);
 int b200_peer_free(void* dev_ptr);
+/* Strided device-to-device copy (rows x width_bytes) between local and/or IPC-mapped peer memory on the
+ * copy engines (cudaMemcpy2DAsync): the pull half of the FSDP weight gather (all-gather before the GEMM,
+ * BASELINE.json case3; reference pattern case5_attention_dense.py:59-67 with rules :109-112) -- weights are
+ * read-only, so pulling needs no cross-rank synchronisation. */
+int b200_peer_copy2d(void* dst, int64_t dst_pitch_bytes, const void* src, int64_t src_pitch_bytes, int64_t width_bytes,
+                     int64_t rows, void* stream);
 int b200_peer_barrier(void* const* flag_ptrs_dev, int rank, int world, uint32_t epoch, void* stream);
 int b200_sum_bf16_partials(const void* src, int64_t src_stride, int nsrc, const void* bias, int64_t cols, void* dst,
                            int64_t n, void* stream);

@@ -40,6 +40,7 @@ EXPORTED_SYMBOLS = (
     "b200_peer_open",
     "b200_peer_close",
     "b200_peer_free",
+    "b200_peer_copy2d",
     "b200_peer_barrier",
     "b200_sum_bf16_partials",
 )
@@ -84,6 +85,7 @@ def load():
     lib.b200_peer_open.argtypes = [vp, ctypes.POINTER(vp)]
     lib.b200_peer_close.argtypes = [vp]
     lib.b200_peer_free.argtypes = [vp]
+    lib.b200_peer_copy2d.argtypes = [vp, i64, vp, i64, i64, i64, vp]
     lib.b200_peer_barrier.argtypes = [vp, i32, i32, ctypes.c_uint32, vp]
     lib.b200_sum_bf16_partials.argtypes = [vp, i64, i32, vp, i64, vp, i64, vp]
     lib.b200_gemm_f32.argtypes = [vp, i64, i64, vp, i64, i64, vp, i64, i64, i32, i32, i32, i32, i32, vp]
@@ -337,3 +339,10 @@ def sum_bf16_partials(src_ptr: int, src_stride: int, nsrc: int, bias, cols: int,
                                            out.numel(), _stream(out))
     _check(rc, "b200_sum_bf16_partials")
     return out
+
+
+def peer_copy2d(dst_ptr: int, dst_pitch: int, src_ptr: int, src_pitch: int, width_bytes: int, rows: int, stream):
+    """Strided D2D / peer copy on the copy engines, enqueued on `stream` (a torch.cuda.Stream)."""
+    rc = load().b200_peer_copy2d(ctypes.c_void_p(dst_ptr), dst_pitch, ctypes.c_void_p(src_ptr), src_pitch, width_bytes,
+                                 rows, ctypes.c_void_p(stream.cuda_stream))
+    _check(rc, "b200_peer_copy2d")

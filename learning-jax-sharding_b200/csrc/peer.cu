@@ -117,6 +117,17 @@ extern "C" int b200_peer_free(void* dev_ptr) {
   return B200_OK;
 }
 
+extern "C" int b200_peer_copy2d(void* dst, int64_t dst_pitch_bytes, const void* src, int64_t src_pitch_bytes,
+                                int64_t width_bytes, int64_t rows, void* stream) {
+  B200_REQUIRE(dst && src && width_bytes > 0 && rows > 0, "b200_peer_copy2d: bad arguments");
+  B200_REQUIRE(dst_pitch_bytes >= width_bytes && src_pitch_bytes >= width_bytes, "b200_peer_copy2d: pitch smaller than row");
+  // device-to-device (local or IPC-mapped peer) strided copy on the copy engines: no SM time
+  B200_CUDA_CHECK(cudaMemcpy2DAsync(dst, static_cast<size_t>(dst_pitch_bytes), src, static_cast<size_t>(src_pitch_bytes),
+                                    static_cast<size_t>(width_bytes), static_cast<size_t>(rows), cudaMemcpyDefault,
+                                    reinterpret_cast<cudaStream_t>(stream)));
+  return B200_OK;
+}
+
 extern "C" int b200_peer_barrier(void* const* flag_ptrs_dev, int rank, int world, uint32_t epoch, void* stream) {
   B200_REQUIRE(flag_ptrs_dev && world >= 1 && world <= 64 && rank >= 0 && rank < world,
                "b200_peer_barrier: bad arguments (world must be 1..64)");

@@ -107,6 +107,52 @@ class TensorParallelFFN:
         return self.y
 
 
+class PeerReduceScatter:
+    """Receive side of the fused GEMM -> reduce-scatter for a row-parallel layer with T rows and N output
+    features over the W ranks of `group`: CUDA-IPC-shared receive buffers (two, alternating per step, each
+    W slots of [T/W, N] bf16), a table of every owner's slot pointers for the GEMM epilogue to push into,
+    a flag barrier and the local f32 reduction of the W received partials."""
+
+    _FLAG_BYTES = 1024
+
+    def __init__(self, T: int, N: int, group, device):
+        import torch.distributed as dist
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        W = self.world
+        if T % W or (T // W) % 256:
+            raise ValueError(f"T={T} must split into {W} blocks of a multiple of 256 rows")
+        self.T, self.N, self.R = T, N, T // W
+        self.slot = self.R * N                                  # elements of one receive slot
+        total = self._FLAG_BYTES + 2 * W * self.slot * 2        # flags + two receive buffers of W slots
+        self.base, handle = capi.peer_alloc(total)
+        mine = torch.tensor(list(handle), dtype=torch.uint8, device=device)
+        handles = [torch.empty_like(mine) for _ in range(W)]
+        dist.all_gather(handles, mine, group=group)
+        self.peer_base = [self.base if p == self.rank else capi.peer_open(bytes(handles[p].cpu().tolist()))
+                          for p in range(W)]
+        self.flag_ptrs = torch.tensor(self.peer_base, dtype=torch.int64, device=device)
+        self.c_ptrs = []
+        for buf in range(2):
+            ptrs = [self.peer_base[p] + self._FLAG_BYTES + ((buf * W + self.rank) * self.slot) * 2 for p in range(W)]
+            self.c_ptrs.append(torch.tensor(ptrs, dtype=torch.int64, device=device))
+        self.buf = 0
+        self.epoch = 0
+        dist.barrier(group=group)
+
+    def push_gemm(self, a: torch.Tensor, w: torch.Tensor):
+        """Partial product a @ w with every finished tile stored into its owner's receive slot (NVLink)."""
+        capi.gemm_bf16_scatter(a, w, self.c_ptrs[self.buf], self.R, (self.rank + 1) % self.world, self.N)
+
+    def finish(self, bias, out: torch.Tensor) -> torch.Tensor:
+        """Barrier (all pushes landed), then out[T/W, N] = bf16(sum of the W partials) (+ bias)."""
+        self.epoch += 1
+        capi.peer_barrier(self.flag_ptrs, self.rank, self.world, self.epoch)
+        src = self.base + self._FLAG_BYTES + (self.buf * self.world * self.slot) * 2
+        capi.sum_bf16_partials(src, self.slot, self.world, bias, self.N, out)
+        self.buf ^= 1
+        return out
+
+
 class FusedTensorParallelFFN:
     """Tensor-parallel FFN whose row-parallel reduction is fused into the second GEMM: every finished tile
     of the partial y is stored from the GEMM epilogue straight into its owner's receive slot over NVLink
@@ -115,56 +161,77 @@ class FusedTensorParallelFFN:
     data path, no token chunking (both GEMMs run at full size).  Same result layout as
     TensorParallelFFN: this rank's sequence block y[rank*T/W : (rank+1)*T/W]."""
 
-    _FLAG_BYTES = 1024
-
     def __init__(self, w1, b1, w2, b2, act: str, T: int, group):
-        import torch.distributed as dist
-        self.dist, self.group = dist, group
-        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         self.w1, self.b1, self.w2, self.b2 = w1, b1, w2, b2
         self.act = _act_code(act, b1 is not None)
         self.d_model, self.F = w1.shape
         self.T = T
-        W = self.world
-        if T % W or (T // W) % 256:
-            raise ValueError(f"T={T} must split into {W} blocks of a multiple of 256 rows")
-        self.R = T // W
         dev = w1.device
-        self.slot = self.R * self.d_model                      # elements of one receive slot
-        total = self._FLAG_BYTES + 2 * W * self.slot * 2       # flags + two receive buffers of W slots
-        self.base, handle = capi.peer_alloc(total)
-        mine = torch.tensor(list(handle), dtype=torch.uint8, device=dev)
-        handles = [torch.empty_like(mine) for _ in range(W)]
-        dist.all_gather(handles, mine, group=group)
-        self.peer_base = []
-        for p in range(W):
-            self.peer_base.append(self.base if p == self.rank else capi.peer_open(bytes(handles[p].cpu().tolist())))
-        self.flag_ptrs = torch.tensor(self.peer_base, dtype=torch.int64, device=dev)
-        self.c_ptrs = []
-        for buf in range(2):
-            ptrs = [self.peer_base[p] + self._FLAG_BYTES + ((buf * W + self.rank) * self.slot) * 2 for p in range(W)]
-            self.c_ptrs.append(torch.tensor(ptrs, dtype=torch.int64, device=dev))
+        self.rs = PeerReduceScatter(T, self.d_model, group, dev)
+        self.world, self.rank = self.rs.world, self.rs.rank
         self.h = torch.empty((T, self.F), dtype=torch.bfloat16, device=dev)
-        self.y = torch.empty((self.R, self.d_model), dtype=torch.bfloat16, device=dev)
-        self.buf = 0
-        self.epoch = 0
-        dist.barrier(group=group)
+        self.y = torch.empty((self.rs.R, self.d_model), dtype=torch.bfloat16, device=dev)
 
     def forward(self, x: torch.Tensor, record=None) -> torch.Tensor:
-        W = self.world
         if record is not None:
             record("start")
         capi.gemm_bf16(x, self.w1, bias=self.b1, epilogue=self.act, out=self.h)
         if record is not None:
             record("gemm1")
-        capi.gemm_bf16_scatter(self.h, self.w2, self.c_ptrs[self.buf], self.R, (self.rank + 1) % W, self.d_model)
+        self.rs.push_gemm(self.h, self.w2)
         if record is not None:
             record("gemm2")
-        self.epoch += 1
-        capi.peer_barrier(self.flag_ptrs, self.rank, W, self.epoch)
-        src = self.base + self._FLAG_BYTES + (self.buf * W * self.slot) * 2
-        capi.sum_bf16_partials(src, self.slot, W, self.b2, self.d_model, self.y)
-        self.buf ^= 1
+        return self.rs.finish(self.b2, self.y)
+
+
+class ShardedMHA:
+    """Multi-head attention layer of the reference module (case6_attention.py:93-143) with heads sharded
+    over the `group` ranks (the BASELINE.json case6 layout): to_q/to_k/to_v column-parallel
+    and fused into ONE [M, 3*Hl*D] GEMM, attention on the local heads straight out of that buffer (strided
+    q/k/v views, no transpose), to_out_0 row-parallel with the fused push reduce-scatter (or a plain GEMM +
+    bias on one GPU).  x: [B, S, M] bf16 replicated over the group; returns this rank's sequence block of y
+    flattened to [B*S/W, M]."""
+
+    def __init__(self, wq, wk, wv, wo, bo, heads_local: int, dim_head: int, B: int, S: int, causal: bool, group=None):
+        self.Hl, self.D, self.B, self.S, self.causal = heads_local, dim_head, B, S, causal
+        self.wqkv = torch.cat([wq, wk, wv], dim=1).contiguous()        # [M, 3*Hl*D]
+        self.wo, self.bo = wo, bo
+        self.M = wq.shape[0]
+        dev = wq.device
+        T = B * S
+        inner = heads_local * dim_head
+        self.qkv = torch.empty((T, 3 * inner), dtype=torch.bfloat16, device=dev)
+        self.o = torch.empty((T, inner), dtype=torch.bfloat16, device=dev)
+        self.rs = None
+        self.world = 1
+        if group is not None:
+            import torch.distributed as dist
+            self.world = dist.get_world_size(group)
+        if self.world > 1:
+            self.rs = PeerReduceScatter(T, self.M, group, dev)
+            self.y = torch.empty((self.rs.R, self.M), dtype=torch.bfloat16, device=dev)
+        else:
+            self.y = torch.empty((T, self.M), dtype=torch.bfloat16, device=dev)
+
+    def forward(self, x: torch.Tensor, record=None) -> torch.Tensor:
+        B, S, Hl, D = self.B, self.S, self.Hl, self.D
+        inner = Hl * D
+        if record is not None:
+            record("start")
+        capi.gemm_bf16(x.reshape(B * S, self.M), self.wqkv, out=self.qkv)                  # :96-99
+        if record is not None:
+            record("qkv")
+        q, k, v = (self.qkv[:, i * inner:(i + 1) * inner].view(B, S, Hl, D) for i in range(3))   # :109-112
+        capi.attention_fwd(q, k, v, scale=D ** -0.5, causal=self.causal, out=self.o.view(B, S, Hl, D))   # :121-135
+        if record is not None:
+            record("attn")
+        if self.rs is None:
+            capi.gemm_bf16(self.o, self.wo, bias=self.bo, epilogue=capi.EPI_BIAS, out=self.y)           # :139
+        else:
+            self.rs.push_gemm(self.o, self.wo)
+            self.rs.finish(self.bo, self.y)
+        if record is not None:
+            record("out")
         return self.y
 
 
@@ -228,6 +295,90 @@ class FsdpFFN:
         return self.y
 
 
+class PeerGatherFFN:
+    """FSDP layout without NCCL on the data path: every rank keeps its dim0-shard of W1 and W2 in
+    CUDA-IPC-shared memory; a forward pass PULLS the other ranks' shards straight out of their HBM with
+    copy-engine peer copies (no SM time, no cross-rank synchronisation -- weights are read-only), one
+    column chunk at a time on side streams, while the GEMM of the previous chunk runs.  Pull order is
+    staggered by rank so every source serves one reader at a time."""
+
+    def __init__(self, w1_shard, b1, w2_shard, b2, act: str, T_local: int, group, chunks: int = 4, copy_streams: int = 4):
+        import torch.distributed as dist
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        W = self.world
+        self.b1, self.b2 = b1, b2
+        self.act = _act_code(act, b1 is not None)
+        self.k1, self.F = w1_shard.shape            # rows of W1 held here, d_ff
+        self.k2, self.d_model = w2_shard.shape      # rows of W2 held here, d_model
+        self.T = T_local
+        self.chunks = chunks
+        dev = w1_shard.device
+        n1, n2 = w1_shard.numel() * 2, w2_shard.numel() * 2
+        self.base, handle = capi.peer_alloc(n1 + n2)
+        # place the shards in the shared allocation
+        capi.peer_copy2d(self.base, n1, w1_shard.data_ptr(), n1, n1, 1, torch.cuda.current_stream(dev))
+        capi.peer_copy2d(self.base + n1, n2, w2_shard.data_ptr(), n2, n2, 1, torch.cuda.current_stream(dev))
+        torch.cuda.synchronize(dev)
+        mine = torch.tensor(list(handle), dtype=torch.uint8, device=dev)
+        handles = [torch.empty_like(mine) for _ in range(W)]
+        dist.all_gather(handles, mine, group=group)
+        self.peer_base = [self.base if p == self.rank else capi.peer_open(bytes(handles[p].cpu().tolist()))
+                          for p in range(W)]
+        self.n1 = n1
+        self.w1g = torch.empty((self.k1 * W, self.F), dtype=torch.bfloat16, device=dev)
+        self.w2g = torch.empty((self.k2 * W, self.d_model), dtype=torch.bfloat16, device=dev)
+        self.h = torch.empty((T_local, self.F), dtype=torch.bfloat16, device=dev)
+        self.y = torch.empty((T_local, self.d_model), dtype=torch.bfloat16, device=dev)
+        self.streams = [torch.cuda.Stream(device=dev) for _ in range(copy_streams)]
+        self.ready = [[torch.cuda.Event() for _ in range(copy_streams)] for _ in range(2 * chunks)]
+        dist.barrier(group=group)
+
+    def _pull(self, which: int, j: int, main):
+        """Enqueue the pulls of column chunk j of weight `which` (0 = W1, 1 = W2) from every rank."""
+        W, C = self.world, self.chunks
+        rows, cols = (self.k1, self.F) if which == 0 else (self.k2, self.d_model)
+        dst = self.w1g if which == 0 else self.w2g
+        cw = cols // C
+        for i in range(W):
+            p = (self.rank + 1 + i) % W                       # own shard last
+            st = self.streams[i % len(self.streams)]
+            src = self.peer_base[p] + (0 if which == 0 else self.n1) + j * cw * 2
+            capi.peer_copy2d(dst.data_ptr() + (p * rows * cols + j * cw) * 2, cols * 2, src, cols * 2, cw * 2, rows, st)
+        for k, st in enumerate(self.streams):
+            self.ready[which * C + j][k].record(st)
+
+    def forward(self, x: torch.Tensor, record=None) -> torch.Tensor:
+        C = self.chunks
+        main = torch.cuda.current_stream(x.device)
+        for st in self.streams:
+            st.wait_stream(main)                              # the previous step's GEMMs have read w1g / w2g
+        for j in range(C):
+            self._pull(0, j, main)
+        for j in range(C):
+            self._pull(1, j, main)
+        fc, dc = self.F // C, self.d_model // C
+        for j in range(C):
+            for ev in self.ready[j]:
+                main.wait_event(ev)
+            if record is not None:
+                record("start")
+            b = self.b1[j * fc:(j + 1) * fc] if self.b1 is not None else None
+            capi.gemm_bf16(x, self.w1g[:, j * fc:(j + 1) * fc], bias=b, epilogue=self.act, out=self.h[:, j * fc:(j + 1) * fc])
+            if record is not None:
+                record("gemm1")
+        for j in range(C):
+            for ev in self.ready[C + j]:
+                main.wait_event(ev)
+            if record is not None:
+                record("start")
+            b = self.b2[j * dc:(j + 1) * dc] if self.b2 is not None else None
+            capi.gemm_bf16(self.h, self.w2g[:, j * dc:(j + 1) * dc], bias=b,
+                           epilogue=capi.EPI_BIAS if b is not None else capi.EPI_NONE, out=self.y[:, j * dc:(j + 1) * dc])
+            if record is not None:
+                record("gemm2")
+        return self.y
+
+
 # ------------------------------------------------------------------------ bench harness glue
 def _synthetic(shape, seed, kind, fan_in=None, device="cuda"):
     """Seeded synthetic tensors of SURVEY.md §8d, generated on the host like the oracle's."""
@@ -262,8 +413,19 @@ class FFNBench:
         if self.mode == "fsdp":
             tl, kl1, kl2 = T // world, d // world, f // world
             self.x_host = x[rank * tl:(rank + 1) * tl].contiguous().pin_memory()
-            self.layer = FsdpFFN(w1[rank * kl1:(rank + 1) * kl1].to(dev), b1.to(dev), w2[rank * kl2:(rank + 1) * kl2].to(dev),
-                                 b2.to(dev), act, tl, group, chunks=chunks)
+            shard = (w1[rank * kl1:(rank + 1) * kl1].contiguous().to(dev), b1.to(dev),
+                     w2[rank * kl2:(rank + 1) * kl2].contiguous().to(dev), b2.to(dev))
+            self.layer = None
+            if os.environ.get("B200_FSDP_COLLECTIVE", "peer") == "peer":
+                try:
+                    self.layer = PeerGatherFFN(*shard, act, tl, group, chunks=chunks)
+                    self.collective = "copy-engine pulls of weight column chunks from peer HBM over NVLink, overlapped with GEMMs"
+                except Exception as e:   # noqa: BLE001
+                    if rank == 0:
+                        print(f"[bench] peer gather unavailable ({e!r}); using NCCL", file=sys.stderr, flush=True)
+            if self.layer is None:
+                self.layer = FsdpFFN(*shard, act, tl, group, chunks=chunks)
+                self.collective = "NCCL all-gather of weight column chunks on a side stream"
             self.T_in, self.T_out = tl, tl
         else:
             fl = f // world
@@ -378,45 +540,110 @@ class FFNBench:
         return None
 
 
-def bench_attention(args, cfg, rank, world, dev, metric, unit, peaks, sampler, attn_flops):
-    """Measurement aid for the attention configs (case5 / case6 of BASELINE.json): attention core and
-    core + projections on one GPU; head-sharded over `world` GPUs when launched under torchrun."""
+def attention_mesh(world: int):
+    """(data, model) mesh for the attention configs at `world` GPUs: (1,1), (1,2), (2,2), (2,4)."""
+    return {1: (1, 1), 2: (1, 2), 4: (2, 2), 8: (2, 4)}.get(world, (1, world))
+
+
+def run_attention_workload(cfg, rank, world, dev, steps, warmup):
+    """The MHA layer of BASELINE.json's case5 / case6 configs (projections + attention core + out-projection)
+    on a (data x model) mesh: batch over 'data', heads over 'model' (fused push reduce-scatter for the
+    row-parallel out-projection).  Returns timing / FLOP figures (max over ranks)."""
     B, S, H, D, M = cfg["batch"], cfg["seq"], cfg["heads"], cfg["dim_head"], cfg["d_model"]
     causal = cfg["causal"]
-    if H % world:
-        raise SystemExit(f"{H} heads do not split over {world} GPUs")
-    hl = H // world
-    q, k, v = (torch.randn((B, S, hl, D), device=dev, dtype=torch.float32).to(torch.bfloat16) for _ in range(3))
-    o = torch.empty_like(q)
-    for _ in range(args.warmup):
-        capi.attention_fwd(q, k, v, causal=causal, out=o)
-    torch.cuda.synchronize(dev)
-    sampler.start()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    l0 = capi.launch_count()
-    e0.record()
-    for _ in range(args.steps):
-        capi.attention_fwd(q, k, v, causal=causal, out=o)
-    e1.record()
-    torch.cuda.synchronize(dev)
-    clocks = sampler.stop()
-    ms = e0.elapsed_time(e1) / args.steps
+    d_ax, m_ax = attention_mesh(world)
+    if B % d_ax or H % m_ax:
+        raise SystemExit(f"batch {B} / heads {H} do not split over mesh {d_ax}x{m_ax}")
+    group = None
+    dist = None
     if world > 1:
         import torch.distributed as dist
-        t = torch.tensor([ms], device=dev)
+        mine = None
+        for g in range(d_ax):
+            ranks = list(range(g * m_ax, (g + 1) * m_ax))
+            pg = dist.new_group(ranks=ranks) if m_ax > 1 else None
+            if rank in ranks:
+                mine = pg
+        group = mine
+    Bl, Hl = B // d_ax, H // m_ax
+    m_rank = rank % m_ax
+    gen = torch.Generator(device=dev).manual_seed(1234 + rank // m_ax)        # same x inside a model group
+    x = torch.randn((Bl, S, M), device=dev, generator=gen, dtype=torch.float32).to(torch.bfloat16)
+    wgen = torch.Generator(device=dev).manual_seed(99)                         # same weights on every rank
+
+    def weight(rows, cols, fan_in):
+        return (torch.randn((rows, cols), device=dev, generator=wgen, dtype=torch.float32) / fan_in ** 0.5).to(torch.bfloat16)
+
+    inner = H * D
+    wq, wk, wv = weight(M, inner, M), weight(M, inner, M), weight(M, inner, M)
+    wo = weight(inner, M, inner)
+    bo = (torch.randn((M,), device=dev, generator=wgen, dtype=torch.float32) * 0.02).to(torch.bfloat16)
+    cs = slice(m_rank * Hl * D, (m_rank + 1) * Hl * D)
+    layer = ShardedMHA(wq[:, cs].contiguous(), wk[:, cs].contiguous(), wv[:, cs].contiguous(), wo[cs].contiguous(), bo,
+                       Hl, D, Bl, S, causal, group if m_ax > 1 else None)
+    del wq, wk, wv, wo
+    for _ in range(warmup):
+        layer.forward(x)
+    torch.cuda.synchronize(dev)
+    if dist is not None:
+        dist.barrier()
+        torch.cuda.synchronize(dev)
+    events = []
+
+    def record(tag):
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record()
+        events.append((tag, ev))
+
+    l0 = capi.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        layer.forward(x, record=record)
+    e1.record()
+    torch.cuda.synchronize(dev)
+    if dist is not None:
+        dist.barrier()
+    ms = e0.elapsed_time(e1) / steps
+    parts = {"qkv": 0.0, "attn": 0.0, "out": 0.0}
+    prev = None
+    for tag, ev in events:
+        if tag != "start":
+            parts[tag] += prev.elapsed_time(ev)
+        prev = ev
+    parts = {k: v / steps for k, v in parts.items()}
+    if dist is not None:
+        t = torch.tensor([ms, parts["qkv"], parts["attn"], parts["out"]], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
-    core, proj = attn_flops(cfg)
-    if rank == 0:
-        val = core / (ms * 1e-3) / 1e12
-        print(json.dumps({
-            "metric": metric, "value": val, "unit": unit, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16",
-            "data": "synthetic",
-            "config": {"workload": args.workload + " (attention core only)", "batch": B, "seq_len": S, "heads": H,
-                       "dim_head": D, "causal": causal, "parallelism": f"heads/{world}", "flops_per_step": core},
-            "clocks": clocks, "gpu_launches": int(capi.launch_count() - l0),
-            "roofline": {"bound": "tensor", "kernel": "attention_fwd_kernel", "achieved": val / world,
-                         "peak": peaks["bf16_burst"], "unit": unit, "frac": val / world / peaks["bf16_burst"],
-                         "peak_source": peaks["source"], "traffic": None},
-            "cpu_baseline": None, "e2e": None}), flush=True)
+        ms, parts = float(t[0]), {"qkv": float(t[1]), "attn": float(t[2]), "out": float(t[3])}
+    core = 2.0 * B * H * S * (S + 1) * D if causal else 4.0 * B * H * S * S * D
+    proj = 8.0 * B * S * M * inner
+    return {"ms_per_step": ms, "parts_ms": parts, "core_flops": core, "proj_flops": proj, "mesh": (d_ax, m_ax),
+            "launches": int(capi.launch_count() - l0), "steps": steps}
+
+
+def bench_attention(args, cfg, rank, world, dev, metric, unit, peaks, sampler, attn_flops):
+    """`bench.py --workload case5_attention_dense|case6_attention`: the full MHA layer at the config shape."""
+    sampler.start()
+    r = run_attention_workload(cfg, rank, world, dev, args.steps, args.warmup)
+    clocks = sampler.stop()
+    if rank != 0:
+        return
+    total = r["core_flops"] + r["proj_flops"]
+    val = total / (r["ms_per_step"] * 1e-3) / 1e12
+    core_tf = r["core_flops"] / (r["parts_ms"]["attn"] * 1e-3) / 1e12 / world
+    d_ax, m_ax = r["mesh"]
+    print(json.dumps({
+        "metric": metric, "value": val, "unit": unit, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": args.workload, "batch": cfg["batch"], "seq_len": cfg["seq"], "heads": cfg["heads"],
+                   "dim_head": cfg["dim_head"], "d_model": cfg["d_model"], "causal": cfg["causal"],
+                   "parallelism": f"mesh data x model = {d_ax}x{m_ax} (batch over data, heads over model)",
+                   "flops_per_step": total, "core_flops": r["core_flops"], "proj_flops": r["proj_flops"],
+                   "parts_ms": r["parts_ms"]},
+        "clocks": clocks, "gpu_launches": r["launches"],
+        "roofline": {"bound": "tensor", "kernel": "attention_fwd2_kernel (per GPU, attention core only)",
+                     "achieved": core_tf, "peak": peaks["bf16_burst"], "unit": unit,
+                     "frac": core_tf / peaks["bf16_burst"], "peak_source": peaks["source"], "traffic": None},
+        "cpu_baseline": None, "e2e": None}), flush=True)

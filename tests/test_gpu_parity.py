@@ -324,3 +324,21 @@ def test_gemm_row_block_scatter_and_partial_sum(ljs):
     capi.sum_bf16_partials(pd.data_ptr(), R * N, W, _dev(bias), N, out)
     ref = (parts.float().sum(0).to(torch.bfloat16).float() + bias.float()).to(torch.bfloat16)
     torch.testing.assert_close(out.cpu().float(), ref.float(), rtol=1e-2, atol=1e-2)
+
+
+@pytest.mark.parametrize("causal", [False, True])
+def test_sharded_mha_layer_one_gpu(ljs, causal):
+    """layers.ShardedMHA (fused qkv projection -> attention on strided views -> out projection) against the
+    oracle's FlaxAttention restatement."""
+    from learning_jax_sharding_b200 import layers
+    B, S, M, H, D = 2, 384, 512, 4, 128
+    x = rm.synthetic((B, S, M), 80)
+    params = {"to_q": rm.synthetic((M, H * D), 81, "weight"), "to_k": rm.synthetic((M, H * D), 82, "weight"),
+              "to_v": rm.synthetic((M, H * D), 83, "weight"),
+              "to_out_0": (rm.synthetic((H * D, M), 84, "weight"), rm.synthetic((M,), 85, "bias"))}
+    bf = lambda t: _dev(t, torch.bfloat16)
+    layer = layers.ShardedMHA(bf(params["to_q"]), bf(params["to_k"]), bf(params["to_v"]), bf(params["to_out_0"][0]),
+                              bf(params["to_out_0"][1]), H, D, B, S, causal)
+    y = layer.forward(bf(x)).cpu().reshape(B, S, M)
+    want = rm.mha_forward(x, params, H, D, causal)
+    torch.testing.assert_close(y.float(), want.float(), **BF16_TOL)

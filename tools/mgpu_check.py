@@ -53,6 +53,27 @@ def main():
     good = bool((err <= 2e-2 * want[rank * blk:(rank + 1) * blk].abs() + 2e-2).all())
     print(f"[rank {rank}] fused TP (peer-memory push): max_abs={err.max().item():.3e} {'OK' if good else 'FAIL'}", flush=True)
     ok &= good
+    # head-sharded MHA layer: fused qkv GEMM, local-head attention, row-parallel out-projection with the push reduce-scatter
+    Bm, Sm, Mm, Hm, Dm = 2, 1024, 512, 8, 64
+    xm = rm.synthetic((Bm, Sm, Mm), 20)
+    pm = {"to_q": rm.synthetic((Mm, Hm * Dm), 21, "weight"), "to_k": rm.synthetic((Mm, Hm * Dm), 22, "weight"),
+          "to_v": rm.synthetic((Mm, Hm * Dm), 23, "weight"),
+          "to_out_0": (rm.synthetic((Hm * Dm, Mm), 24, "weight"), rm.synthetic((Mm,), 25, "bias"))}
+    want_m = rm.mha_forward(xm, pm, Hm, Dm, causal=True).float().reshape(Bm * Sm, Mm)
+    hl = Hm // world
+    cs = slice(rank * hl * Dm, (rank + 1) * hl * Dm)
+    mha = layers.ShardedMHA(bf(pm["to_q"][:, cs].contiguous()), bf(pm["to_k"][:, cs].contiguous()),
+                            bf(pm["to_v"][:, cs].contiguous()), bf(pm["to_out_0"][0][cs].contiguous()),
+                            bf(pm["to_out_0"][1]), hl, Dm, Bm, Sm, True, dist.group.WORLD)
+    for it in range(3):
+        ym = mha.forward(bf(xm))
+    torch.cuda.synchronize()
+    blk = Bm * Sm // world
+    ref = want_m[rank * blk:(rank + 1) * blk]
+    err = (ym.cpu().float() - ref).abs()
+    good = bool((err <= 2e-2 * ref.abs() + 2e-2).all())
+    print(f"[rank {rank}] head-sharded MHA (causal): max_abs={err.max().item():.3e} {'OK' if good else 'FAIL'}", flush=True)
+    ok &= good
     # FSDP: tokens over ranks, weights dim0-sharded, all-gather in column chunks
     tl, k1, k2 = T // world, d // world, f // world
     fs = layers.FsdpFFN(bf(w1[rank * k1:(rank + 1) * k1].contiguous()), bf(b1), bf(w2[rank * k2:(rank + 1) * k2].contiguous()),
@@ -63,6 +84,15 @@ def main():
     err = (y.cpu().float() - want[rank * tl:(rank + 1) * tl]).abs()
     good = bool((err <= 2e-2 * want[rank * tl:(rank + 1) * tl].abs() + 2e-2).all())
     print(f"[rank {rank}] FSDP: max_abs={err.max().item():.3e} {'OK' if good else 'FAIL'}", flush=True)
+    ok &= good
+    pg = layers.PeerGatherFFN(bf(w1[rank * k1:(rank + 1) * k1].contiguous()), bf(b1), bf(w2[rank * k2:(rank + 1) * k2].contiguous()),
+                              bf(b2), "gelu_tanh", tl, dist.group.WORLD, chunks=4)
+    for it in range(3):
+        y = pg.forward(bf(x[rank * tl:(rank + 1) * tl].contiguous()))
+    torch.cuda.synchronize()
+    err = (y.cpu().float() - want[rank * tl:(rank + 1) * tl]).abs()
+    good = bool((err <= 2e-2 * want[rank * tl:(rank + 1) * tl].abs() + 2e-2).all())
+    print(f"[rank {rank}] FSDP peer-pull gather: max_abs={err.max().item():.3e} {'OK' if good else 'FAIL'}", flush=True)
     ok &= good
     # the generic host layer on a real 1 x world mesh: nn.ffn with NCCL collectives
     P = ljs.PartitionSpec
