@@ -55,6 +55,7 @@ struct GemmParams {
   // to c_block_ptrs[block] (a peer GPU's receive slot, or local memory) at row m % m_rows_per_block.
   void* const* c_block_ptrs;
   int m_rows_per_block, m_block_rot, m_num_blocks;
+  int num_stages;   // smem ring depth actually used (<= Cfg::kStages); tuning experiments only
 };
 
 __device__ __forceinline__ float gelu_tanh_f(float x) {
@@ -179,7 +180,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               tma_load_2d_cg2(sb + c * (kBK * 128), &tmB, &full_bar[stage], n0 + c * 64, k0);
           }
         }
-        if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+        if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1 && lane == 0 && leader) {
@@ -217,7 +218,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           if (G == 1) mma_commit(&tmem_full_bar[acc]);
           else mma_commit_cg2(&tmem_full_bar[acc], 0x3);
         }
-        if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+        if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
       }
       if (++acc == Cfg::kAccStages) { acc = 0; acc_phase ^= 1; }
     }
@@ -362,6 +363,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 static int g_force_cta_group = 0;   // 0 = heuristic; 1 / 2 force (set through b200_gemm_set_tuning)
 static int g_force_bn = 0;
 static int g_group_m = 0;   // 0 = heuristic below
+static int g_max_stages = 0;   // 0 = all the stages that fit
 
 template <int BN, int G, bool kBKmajor>
 static int launch_gemm(const void* A, int64_t lda, const void* B, int64_t ldb, const GemmParams& p0,
@@ -370,15 +372,14 @@ static int launch_gemm(const void* A, int64_t lda, const void* B, int64_t ldb, c
   GemmParams p = p0;
   p.tiles_m = (p.M + kBM * G - 1) / (kBM * G);
   p.tiles_n = (p.N + BN - 1) / BN;
-  if (g_group_m > 0) {
-    p.group_m = g_group_m;
-  } else {
-    // keep the A panels of one group (group_m row-blocks x K) resident in L2 (~128 MB budget) while the
-    // B panels stream past: measured best 32 at K = 4096, 16 at K = 16384 (profiles/r01_gemm_raster_sweep.log)
-    const int64_t panel_bytes = static_cast<int64_t>(kBM) * G * p.K * 2;
-    int64_t gm = (128ll << 20) / (panel_bytes > 0 ? panel_bytes : 1);
-    p.group_m = static_cast<int>(gm < 4 ? 4 : (gm > 32 ? 32 : gm));
-  }
+  // Ring depth: measured on B200 (profiles/r01_gemm_stage_sweep.log), CTA pairs run fastest with FOUR
+  // 32 KB stages (1348 / 1417 TFLOP/s) and lose 5-15 % with five or six although the smem is there: a deeper
+  // ring lets the CTAs of a wave drift apart in K, which costs L2 locality on the shared A/B panels.
+  int stages = Cfg::kStages;
+  if (G == 2 && stages > 4) stages = 4;
+  if (g_max_stages > 0 && g_max_stages < stages) stages = g_max_stages;
+  p.num_stages = stages;
+  p.group_m = g_group_m > 0 ? g_group_m : 8;   // raster group: flat within noise at 4 stages (r01_gemm_sweep2.log)
   CUtensorMap tmA, tmB;
   {
     uint64_t a_rows = static_cast<uint64_t>(p.M);
@@ -444,6 +445,12 @@ extern "C" int b200_gemm_set_tuning(int cta_group, int block_n) {
     return fail(B200_ERR_INVALID_ARGUMENT, "block_n must be 0, 64, 128 or 256");
   g_force_cta_group = cta_group;
   g_force_bn = block_n;
+  return B200_OK;
+}
+
+extern "C" int b200_gemm_set_max_stages(int stages) {
+  if (stages < 0 || stages > 8) return fail(B200_ERR_INVALID_ARGUMENT, "stages must be in [0, 8]");
+  g_max_stages = stages;
   return B200_OK;
 }
 

@@ -167,6 +167,60 @@ def main():
                           flush=True)
             ms = time_fn(lambda: torch.matmul(a, b, out=out), iters=30)
             print(f"  cublas M={M} N={N} K={K}: {ms:.3f} ms {2 * M * N * K / ms / 1e9:.1f} TFLOP/s", flush=True)
+    elif args.what == "gemm_stages":
+        import ctypes
+        lib = capi.load()
+        lib.b200_gemm_set_max_stages.argtypes = [ctypes.c_int]
+        import statistics
+        for (M, N, K) in [(16384, 16384, 4096), (16384, 4096, 16384)]:
+            a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
+            b = torch.randn(K, N, device="cuda").to(torch.bfloat16)
+            out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+            variants = [(2, 256, st) for st in (2, 3, 4, 5, 6)] + [(1, 256, st) for st in (2, 3, 4)] + [(0, 0, -1)]
+            res = {v: [] for v in variants}
+            for rnd in range(4):                       # interleave variants so clocks / thermals are shared
+                for v in variants:
+                    g, bn, st = v
+                    if st < 0:
+                        ms = time_fn(lambda: torch.matmul(a, b, out=out), iters=10, warmup=2)
+                    else:
+                        capi.set_gemm_tuning(g, bn)
+                        lib.b200_gemm_set_max_stages(st)
+                        ms = time_fn(lambda: capi.gemm_bf16(a, b, out=out), iters=10, warmup=2)
+                    res[v].append(ms)
+            for v in variants:
+                ms = statistics.median(res[v])
+                name = "cublas" if v[2] < 0 else f"g={v[0]} bn={v[1]} stages={v[2]}"
+                print(f"  {name:24s} M={M} N={N} K={K}: {ms:.3f} ms {2 * M * N * K / ms / 1e9:.1f} TFLOP/s", flush=True)
+            lib.b200_gemm_set_max_stages(0)
+    elif args.what == "gemm_sweep2":
+        import ctypes
+        import statistics
+        lib = capi.load()
+        lib.b200_gemm_set_max_stages.argtypes = [ctypes.c_int]
+        for (M, N, K) in [(16384, 16384, 4096), (16384, 4096, 16384), (32768, 12288, 4096), (8192, 8192, 8192)]:
+            a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
+            b = torch.randn(K, N, device="cuda").to(torch.bfloat16)
+            out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+            variants = [(2, 256, 4, gm) for gm in (4, 8, 16, 32, 64)] + [(2, 256, 3, 16), (1, 256, 4, 16), (0, 0, -1, 0)]
+            res = {v: [] for v in variants}
+            for rnd in range(4):
+                for v in variants:
+                    g, bn, st, gm = v
+                    if st < 0:
+                        ms = time_fn(lambda: torch.matmul(a, b, out=out), iters=10, warmup=2)
+                    else:
+                        capi.set_gemm_tuning(g, bn)
+                        capi.set_gemm_group_m(gm)
+                        lib.b200_gemm_set_max_stages(st)
+                        ms = time_fn(lambda: capi.gemm_bf16(a, b, out=out), iters=10, warmup=2)
+                    res[v].append(ms)
+            for v in variants:
+                ms = statistics.median(res[v])
+                name = "cublas" if v[2] < 0 else f"g={v[0]} bn={v[1]} stages={v[2]} group_m={v[3]}"
+                print(f"  {name:36s} M={M} N={N} K={K}: {ms:.3f} ms {2 * M * N * K / ms / 1e9:.1f} TFLOP/s", flush=True)
+            lib.b200_gemm_set_max_stages(0)
+            capi.set_gemm_group_m(0)
     elif args.what == "attn_prof":
         q, k, v = (torch.randn(2, 4096, 16, 128, device="cuda").to(torch.bfloat16) for _ in range(3))
         for _ in range(3):
