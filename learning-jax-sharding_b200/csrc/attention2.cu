@@ -126,17 +126,24 @@ attention_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
 #pragma unroll
       for (int c = 0; c < D / 64; ++c)
         tma_load_4d(sQ + q * Cfg::kQBytes + c * (kA2BM * 128), &tmQ, q_full, c * 64, head, f_base + q * kA2BM, batch);
-    // ring item i: K_j for i = 2j, V_j for i = 2j+1
-    for (int i = 0; i < 2 * n_max; ++i) {
-      const int st = i % Cfg::kStages;
-      const uint32_t ph = (i / Cfg::kStages) & 1;
-      const int t0 = (i >> 1) * kA2BN;
+    // One ring, K running a tile ahead of V:  K_0, K_1, V_0, K_2, V_1, K_3, V_2, ...  K_{j+1} is wanted early
+    // (Q.K^T of the next tile is issued as soon as the softmax has read S), V_j late (after the softmax of
+    // tile j); in this order, with three slots, K_{j+2} reuses V_{j-1}'s slot and V_j reuses K_j's.
+    int item = 0;
+    auto load = [&](const CUtensorMap* tm, int j) {
+      const int st = item % Cfg::kStages;
+      const uint32_t ph = (item / Cfg::kStages) & 1;
+      ++item;
       mbar_wait(&kv_empty[st], ph ^ 1);
       mbar_arrive_expect_tx(&kv_full[st], Cfg::kKVBytes);
-      const CUtensorMap* tm = (i & 1) ? &tmV : &tmK;
 #pragma unroll
       for (int c = 0; c < D / 64; ++c)
-        tma_load_4d(sKV + st * Cfg::kKVBytes + c * (kA2BN * 128), tm, &kv_full[st], c * 64, head, t0, batch);
+        tma_load_4d(sKV + st * Cfg::kKVBytes + c * (kA2BN * 128), tm, &kv_full[st], c * 64, head, j * kA2BN, batch);
+    };
+    if (n_max > 0) load(&tmK, 0);
+    for (int j = 0; j < n_max; ++j) {
+      if (j + 1 < n_max) load(&tmK, j + 1);
+      load(&tmV, j);
     }
   } else if (warp == 1 && lane == 0) {
     // ===================== MMA issuer =====================
@@ -154,10 +161,10 @@ attention_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         // ---- S[q] = Q_q . K_j^T
         if (next_qk[q] < n_tiles[q]) {
           const int j = next_qk[q];
-          const int i = 2 * j, st = i % Cfg::kStages;
+          const int i = j == 0 ? 0 : 2 * j - 1, st = i % Cfg::kStages;      // ring position of K_j
           const uint32_t ph = (i / Cfg::kStages) & 1;
-          const bool s_ok = (j == 0) || mbar_try_wait(&s_free[q], (j - 1) & 1);
-          if (s_ok && mbar_try_wait(&kv_full[st], ph)) {
+          const bool s_ok = (j == 0) || mbar_test_wait(&s_free[q], (j - 1) & 1);
+          if (s_ok && mbar_test_wait(&kv_full[st], ph)) {
             tc_fence_after();
             const uint32_t q_addr = smem_u32(sQ + q * Cfg::kQBytes);
             const uint32_t k_addr = smem_u32(sKV + st * Cfg::kKVBytes);
@@ -179,9 +186,9 @@ attention_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         // ---- O[q] += P_q . V_j
         if (next_pv[q] < next_qk[q]) {
           const int j = next_pv[q];
-          const int i = 2 * j + 1, st = i % Cfg::kStages;
+          const int i = (j + 1 < n_max) ? 2 * j + 2 : 2 * j + 1, st = i % Cfg::kStages;   // ring position of V_j
           const uint32_t ph = (i / Cfg::kStages) & 1;
-          if (mbar_try_wait(&p_full[q], j & 1) && mbar_try_wait(&kv_full[st], ph)) {
+          if (mbar_test_wait(&p_full[q], j & 1) && mbar_test_wait(&kv_full[st], ph)) {
             tc_fence_after();
             const uint32_t p_addr = smem_u32(sP + q * Cfg::kPBytes);
             const uint32_t v_addr = smem_u32(sKV + st * Cfg::kKVBytes);
@@ -250,14 +257,20 @@ attention_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&s_free[q]);
-      if (need_mask) {
+      if (__any_sync(0xffffffffu, need_mask)) {     // warp-uniform: only diagonal / tail tiles pay for masking
+        asm volatile("" ::: "memory");               // keep this a branch (not 128 predicated selects on every tile)
 #pragma unroll
         for (int i = 0; i < 128; ++i)
-          if (i >= limit) s[i] = 0xff800000u;    // -inf
+          if (i >= limit) s[i] = 0xff800000u;        // -inf
       }
-      float mx = -INFINITY;
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};   // four chains instead of one 64-deep one
 #pragma unroll
-      for (int i = 0; i < 128; i += 2) mx = max3(mx, __uint_as_float(s[i]), __uint_as_float(s[i + 1]));
+      for (int i = 0; i < 128; i += 8) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          mx4[c] = max3(mx4[c], __uint_as_float(s[i + 2 * c]), __uint_as_float(s[i + 2 * c + 1]));
+      }
+      const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
       const float m_tile = mx * p.scale_log2;
       float factor = 1.0f;
       bool rescale = false;
@@ -286,24 +299,34 @@ attention_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         }
         tmem_wait_st();
       }
-      const float neg_m = -m_used;
-      float sum0 = 0.f, sum1 = 0.f;
+      // p = exp2(s * scale_log2 - m_used): packed f32x2 FMA / ADD, one MUFU per element, bf16x2 pack
+      const uint64_t scale2 = pack_f32x2(p.scale_log2, p.scale_log2);
+      const uint64_t negm2 = pack_f32x2(-m_used, -m_used);
+      uint64_t sum2[2] = {0ull, 0ull};
+      uint8_t* prow = sPq + row * 128;
+      const uint32_t r7x16 = (row & 7) << 4;
 #pragma unroll
       for (int u = 0; u < 16; ++u) {            // 16-byte unit u = keys [8u, 8u+8)
         uint32_t pk[4];
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
-          const float p0 = exp2_approx(fmaf(__uint_as_float(s[u * 8 + 2 * e]), p.scale_log2, neg_m));
-          const float p1 = exp2_approx(fmaf(__uint_as_float(s[u * 8 + 2 * e + 1]), p.scale_log2, neg_m));
-          sum0 += p0;
-          sum1 += p1;
+          const uint64_t x2 = fma_f32x2(pack_f32x2(__uint_as_float(s[u * 8 + 2 * e]), __uint_as_float(s[u * 8 + 2 * e + 1])),
+                                        scale2, negm2);
+          float x0, x1;
+          unpack_f32x2(x2, x0, x1);
+          const float p0 = exp2_approx(x0), p1 = exp2_approx(x1);
+          sum2[e & 1] = add_f32x2(sum2[e & 1], pack_f32x2(p0, p1));
           pk[e] = pack_bf16x2(p0, p1);
         }
-        const int chunk = u >> 3;
-        uint8_t* dst = sPq + chunk * (kA2BM * 128) + row * 128 + (((u & 7) ^ (row & 7)) << 4);
+        uint8_t* dst = prow + (u >> 3) * (kA2BM * 128) + ((((u & 7) << 4)) ^ r7x16);
         *reinterpret_cast<uint4*>(dst) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
       }
-      l_sum += sum0 + sum1;
+      {
+        float a0, a1, b0, b1;
+        unpack_f32x2(sum2[0], a0, a1);
+        unpack_f32x2(sum2[1], b0, b1);
+        l_sum += (a0 + a1) + (b0 + b1);
+      }
       fence_async_smem();
       tc_fence_before();
       __syncwarp();
