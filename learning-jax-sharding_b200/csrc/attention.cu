@@ -339,14 +339,20 @@ static int launch_attention(const void* Q, const void* K, const void* V, const A
 
 int attention_fwd2_dispatch(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
                             const int64_t* strides, float scale, int causal, cudaStream_t stream);
-static int g_attn_variant = 0;   // 0 = auto, 1 = one query tile per CTA, 2 = two query tiles per CTA
+int attention_fwd3_dispatch(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
+                            const int64_t* strides, float scale, int causal, cudaStream_t stream);
+int attention_fwd4_dispatch(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
+                            const int64_t* strides, float scale, int causal, cudaStream_t stream);
+// 0 = auto; 1 = one query tile per CTA; 2 = two query tiles, 128-key tiles, P through smem; 3 = two query tiles,
+// 64-key tiles, double-buffered S and P; 4 = two query tiles, 128-key tiles, P kept in TMEM (A operand of P.V)
+static int g_attn_variant = 0;
 
 }  // namespace b200
 
 using namespace b200;
 
 extern "C" int b200_attention_set_variant(int variant) {
-  if (variant < 0 || variant > 2) return fail(B200_ERR_INVALID_ARGUMENT, "attention variant must be 0, 1 or 2");
+  if (variant < 0 || variant > 4) return fail(B200_ERR_INVALID_ARGUMENT, "attention variant must be 0..4");
   g_attn_variant = variant;
   return B200_OK;
 }
@@ -369,8 +375,10 @@ extern "C" int b200_attention_fwd(const void* Q, const void* K, const void* V, v
                 reinterpret_cast<uintptr_t>(O)) % 16 == 0,
                "b200_attention_fwd: operands must be 16-byte aligned");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  const bool two_tiles = g_attn_variant == 2 || (g_attn_variant == 0 && Sq > kAttnBM);
-  if (two_tiles) return attention_fwd2_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
+  if (g_attn_variant == 4) return attention_fwd4_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
+  if (g_attn_variant == 3) return attention_fwd3_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
+  if (g_attn_variant == 2 || (g_attn_variant == 0 && Sq > kAttnBM))
+    return attention_fwd2_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
   AttnParams p = {};
   p.O = reinterpret_cast<__nv_bfloat16*>(O);
   p.B = B;

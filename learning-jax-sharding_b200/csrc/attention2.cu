@@ -72,7 +72,7 @@ attention_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
   uint64_t* pv_done = p_full + 2;                       // 2
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(pv_done + 2);
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = uniform_warp_idx();
   const int lane = threadIdx.x & 31;
   const int q_block = p.causal ? (p.num_q_blocks - 1 - blockIdx.x) : blockIdx.x;   // heaviest first
   const int head = blockIdx.y;
@@ -145,12 +145,19 @@ attention_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
       if (j + 1 < n_max) load(&tmK, j + 1);
       load(&tmV, j);
     }
-  } else if (warp == 1 && lane == 0) {
+  } else if (warp == 1) {
     // ===================== MMA issuer =====================
     constexpr uint32_t idesc_qk = make_idesc_bf16(kA2BM, kA2BN, false, false);
     constexpr uint32_t idesc_pv = make_idesc_bf16(kA2BM, D, false, true);
     int next_qk[2] = {0, 0};     // next KV tile whose Q.K^T is to be issued, per query tile
     int next_pv[2] = {0, 0};
+    // descriptors built once; per MMA only constants are added, and the whole warp runs this loop with one
+    // elected lane issuing, so that every operand stays in uniform registers (a 128x128x16 MMA lasts 64 cycles:
+    // the issuing thread must not spend more than that per instruction)
+    const uint64_t q_desc0 = make_smem_desc_sw128(smem_u32(sQ), 16, 1024);
+    const uint64_t p_desc0 = make_smem_desc_sw128(smem_u32(sP), 16, 1024);
+    const uint64_t k_desc0 = make_smem_desc_sw128(smem_u32(sKV), 16, 1024);
+    const uint64_t v_desc0 = make_smem_desc_sw128(smem_u32(sKV), kA2BN * 128, 1024);
     mbar_wait(q_full, 0);
     int remaining = 2 * (n_tiles[0] + n_tiles[1]);
     uint32_t idle = 0;
@@ -166,18 +173,21 @@ attention_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
           const bool s_ok = (j == 0) || mbar_test_wait(&s_free[q], (j - 1) & 1);
           if (s_ok && mbar_test_wait(&kv_full[st], ph)) {
             tc_fence_after();
-            const uint32_t q_addr = smem_u32(sQ + q * Cfg::kQBytes);
-            const uint32_t k_addr = smem_u32(sKV + st * Cfg::kKVBytes);
-            const uint32_t s_tmem = tmem_base + Cfg::kSCol + q * 128;
+            if (elect_one()) {
+              const uint64_t qd = desc_advance(q_desc0, q * Cfg::kQBytes);
+              const uint64_t kd = desc_advance(k_desc0, st * Cfg::kKVBytes);
+              const uint32_t s_tmem = tmem_base + Cfg::kSCol + q * 128;
+              mma_bf16_ss_c<false>(s_tmem, qd, kd, idesc_qk);
 #pragma unroll
-            for (int kk = 0; kk < D / 16; ++kk) {
-              const uint32_t o = (kk >> 2) * (kA2BM * 128) + (kk & 3) * 32;
-              mma_bf16_ss(s_tmem, make_smem_desc_sw128(q_addr + o, 16, 1024),
-                          make_smem_desc_sw128(k_addr + o, 16, 1024), idesc_qk, kk > 0 ? 1u : 0u);
+              for (int kk = 1; kk < D / 16; ++kk) {
+                const uint32_t o = (kk >> 2) * (kA2BM * 128) + (kk & 3) * 32;
+                mma_bf16_ss_c<true>(s_tmem, desc_advance(qd, o), desc_advance(kd, o), idesc_qk);
+              }
+              mma_commit(&s_full[q]);
+              mma_commit(&kv_empty[st]);
+              if (j >= n_tiles[q ^ 1]) mbar_arrive(&kv_empty[st]);   // the other tile never reads K_j
             }
-            mma_commit(&s_full[q]);
-            mma_commit(&kv_empty[st]);
-            if (j >= n_tiles[q ^ 1]) mbar_arrive(&kv_empty[st]);   // the other tile never reads K_j
+            __syncwarp();
             ++next_qk[q];
             --remaining;
             progressed = true;
@@ -190,19 +200,21 @@ attention_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
           const uint32_t ph = (i / Cfg::kStages) & 1;
           if (mbar_test_wait(&p_full[q], j & 1) && mbar_test_wait(&kv_full[st], ph)) {
             tc_fence_after();
-            const uint32_t p_addr = smem_u32(sP + q * Cfg::kPBytes);
-            const uint32_t v_addr = smem_u32(sKV + st * Cfg::kKVBytes);
-            const uint32_t o_tmem = tmem_base + Cfg::kOCol + q * 128;
+            if (elect_one()) {
+              const uint64_t pd = desc_advance(p_desc0, q * Cfg::kPBytes);
+              const uint64_t vd = desc_advance(v_desc0, st * Cfg::kKVBytes);
+              const uint32_t o_tmem = tmem_base + Cfg::kOCol + q * 128;
+              if (j == 0) mma_bf16_ss_c<false>(o_tmem, pd, vd, idesc_pv);
+              else mma_bf16_ss_c<true>(o_tmem, pd, vd, idesc_pv);
 #pragma unroll
-            for (int kk = 0; kk < kA2BN / 16; ++kk) {
-              const uint64_t da =
-                  make_smem_desc_sw128(p_addr + (kk >> 2) * (kA2BM * 128) + (kk & 3) * 32, 16, 1024);
-              const uint64_t db = make_smem_desc_sw128(v_addr + kk * (16 * 128), kA2BN * 128, 1024);
-              mma_bf16_ss(o_tmem, da, db, idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
+              for (int kk = 1; kk < kA2BN / 16; ++kk)
+                mma_bf16_ss_c<true>(o_tmem, desc_advance(pd, (kk >> 2) * (kA2BM * 128) + (kk & 3) * 32),
+                                    desc_advance(vd, kk * (16 * 128)), idesc_pv);
+              mma_commit(&pv_done[q]);
+              mma_commit(&kv_empty[st]);
+              if (j >= n_tiles[q ^ 1]) mbar_arrive(&kv_empty[st]);
             }
-            mma_commit(&pv_done[q]);
-            mma_commit(&kv_empty[st]);
-            if (j >= n_tiles[q ^ 1]) mbar_arrive(&kv_empty[st]);
+            __syncwarp();
             ++next_pv[q];
             --remaining;
             progressed = true;

@@ -1,0 +1,409 @@
+// Attention forward, two query tiles per CTA, P KEPT IN TENSOR MEMORY: the bf16 probabilities are written
+// with tcgen05.st over the first 64 columns of the score tile they came from and feed P.V as the A operand
+// straight from TMEM (tcgen05.mma with A in TMEM).  Same math and layout as attention.cu
+// (reference order case6_attention.py:121-135).
+//
+// Why: with 128x128x16 MMAs fed from shared memory, Q.K^T and P.V each read 8 KB of smem per 64-cycle
+// instruction = 128 B/clk, the whole smem bandwidth of the SM, on top of the TMA fills and the P stores; the
+// smem-P variant (attention2.cu) tops out near 45 % tensor-pipe activity for that reason (ablation:
+// profiles/r01_attention_ablation.log).  With P in TMEM, P.V reads only V from smem, the P round trip through
+// smem disappears, and the freed 64 KB deepen the K/V ring from 3 to 5 tiles.
+//
+//   warp 0        TMA producer: both Q tiles once, then K_0,K_1,V_0,K_2,V_1,... through one smem ring
+//   warp 1        MMA issuer (whole warp polls, one elected lane issues). Per query tile the order is fixed:
+//                 S=Q.K^T(j) ; [softmax] ; O+=P.V(j) ; S=Q.K^T(j+1) ; ...  (P aliases S, and tcgen05 executes one
+//                 thread's MMAs in issue order), the two query tiles alternate on the tensor pipe
+//   warp 2        TMEM allocator (S0,S1: 2 x 128 columns, P_q = first 64 columns of S_q; O0,O1: 2 x D columns)
+//   warps 4..7    softmax / correction / epilogue of query tile 0 (one row per thread)
+//   warps 8..11   the same for query tile 1
+#include <cuda.h>
+#include <math.h>
+
+#include "host_common.h"
+#include "sm100_ptx.cuh"
+
+namespace b200 {
+
+constexpr int kA4BM = 128;      // rows per query tile
+constexpr int kA4BN = 128;      // keys per KV tile
+constexpr int kA4Threads = 384;
+constexpr float kA4Rescale = 8.0f;
+
+template <int D>
+struct Attn4Cfg {
+  static constexpr int kQBytes = kA4BM * D * 2;          // one query tile
+  static constexpr int kKVBytes = kA4BN * D * 2;         // one K or V tile
+  static constexpr int kBudget = 227 * 1024 - 1024 - 512 - 2 * kQBytes;
+  static constexpr int kStages = kBudget / kKVBytes > 8 ? 8 : kBudget / kKVBytes;
+  static constexpr int kSmemBytes = 2 * kQBytes + kStages * kKVBytes + 1024 + 512;
+  static constexpr int kTmemCols = 512;
+  static constexpr int kSCol = 0;       // S[q] at kSCol + 128 q; P[q] = its first 64 columns (bf16 pairs)
+  static constexpr int kOCol = 256;     // O[q] at kOCol + 128 q
+};
+
+struct Attn4Params {
+  __nv_bfloat16* O;
+  int Sq, Sk;
+  int64_t o_stride_b, o_stride_s, o_stride_h;
+  float scale_log2;
+  int causal;
+  int num_q_blocks;
+};
+
+__device__ __forceinline__ float max3g(float a, float b, float c) {
+  float r;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+  return r;
+}
+
+template <int D>
+__global__ void __launch_bounds__(kA4Threads, 1)
+attention_fwd4_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                      const __grid_constant__ CUtensorMap tmV, const Attn4Params p) {
+  using Cfg = Attn4Cfg<D>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;                                   // [2][128][D]
+  uint8_t* sKV = sQ + 2 * Cfg::kQBytes;                 // ring
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sKV + Cfg::kStages * Cfg::kKVBytes);
+  uint64_t* q_full = bars;                              // 1
+  uint64_t* kv_full = bars + 1;                         // kStages
+  uint64_t* kv_empty = kv_full + Cfg::kStages;          // kStages (2 arrivals: one per query tile)
+  uint64_t* s_full = kv_empty + Cfg::kStages;           // 2
+  uint64_t* p_full = s_full + 2;                        // 2 (4 warp arrivals)
+  uint64_t* o_done = p_full + 2;                        // 2 (after the last P.V of a query tile)
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(o_done + 2);
+
+  const int warp = uniform_warp_idx();
+  const int lane = threadIdx.x & 31;
+  const int q_block = p.causal ? (p.num_q_blocks - 1 - blockIdx.x) : blockIdx.x;   // heaviest first
+  const int head = blockIdx.y;
+  const int batch = blockIdx.z;
+  const int f_base = q_block * 2 * kA4BM;
+  const int off = p.Sk - p.Sq;
+  // KV tiles each query tile needs (0 if the tile lies beyond Sq)
+  int n_tiles[2];
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    const int f0 = f_base + q * kA4BM;
+    int kv_len = p.Sk;
+    if (p.causal) kv_len = min(p.Sk, f0 + kA4BM + off);
+    n_tiles[q] = f0 < p.Sq ? (kv_len + kA4BN - 1) / kA4BN : 0;
+  }
+  const int n_max = max(n_tiles[0], n_tiles[1]);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmK);
+    tma_prefetch_desc(&tmV);
+  }
+  if (warp == 1 && lane == 0) {
+    mbar_init(q_full, 1);
+    for (int s = 0; s < Cfg::kStages; ++s) {
+      mbar_init(&kv_full[s], 1);
+      mbar_init(&kv_empty[s], 2);
+    }
+    for (int q = 0; q < 2; ++q) {
+      mbar_init(&s_full[q], 1);
+      mbar_init(&p_full[q], 4);
+      mbar_init(&o_done[q], 1);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc<Cfg::kTmemCols>(tmem_ptr_smem);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  // register re-split: the control warp group needs few, each softmax thread keeps a 128-wide score row
+  if (warp < 4) {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+  if (warp == 0 && lane == 0) {
+    // ===================== TMA producer =====================
+    mbar_arrive_expect_tx(q_full, 2 * Cfg::kQBytes);
+#pragma unroll
+    for (int q = 0; q < 2; ++q)
+#pragma unroll
+      for (int c = 0; c < D / 64; ++c)
+        tma_load_4d(sQ + q * Cfg::kQBytes + c * (kA4BM * 128), &tmQ, q_full, c * 64, head, f_base + q * kA4BM, batch);
+    // One ring, K running a tile ahead of V:  K_0, K_1, V_0, K_2, V_1, K_3, V_2, ...  K_{j+1} is wanted early
+    // (Q.K^T of the next tile is issued as soon as the softmax has read S), V_j late (after the softmax of
+    // tile j); in this order, with three slots, K_{j+2} reuses V_{j-1}'s slot and V_j reuses K_j's.
+    int item = 0;
+    auto load = [&](const CUtensorMap* tm, int j) {
+      const int st = item % Cfg::kStages;
+      const uint32_t ph = (item / Cfg::kStages) & 1;
+      ++item;
+      mbar_wait(&kv_empty[st], ph ^ 1);
+      mbar_arrive_expect_tx(&kv_full[st], Cfg::kKVBytes);
+#pragma unroll
+      for (int c = 0; c < D / 64; ++c)
+        tma_load_4d(sKV + st * Cfg::kKVBytes + c * (kA4BN * 128), tm, &kv_full[st], c * 64, head, j * kA4BN, batch);
+    };
+    if (n_max > 0) load(&tmK, 0);
+    for (int j = 0; j < n_max; ++j) {
+      if (j + 1 < n_max) load(&tmK, j + 1);
+      load(&tmV, j);
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    constexpr uint32_t idesc_qk = make_idesc_bf16(kA4BM, kA4BN, false, false);
+    constexpr uint32_t idesc_pv = make_idesc_bf16(kA4BM, D, false, true);
+    // per query tile: next_qk[q] == next_pv[q]      -> Q.K^T(next_qk) is the next op of that tile
+    //                 next_qk[q] == next_pv[q] + 1  -> P.V(next_pv) is (it waits for the softmax)
+    int next_qk[2] = {0, 0};
+    int next_pv[2] = {0, 0};
+    const uint64_t q_desc0 = make_smem_desc_sw128(smem_u32(sQ), 16, 1024);
+    const uint64_t k_desc0 = make_smem_desc_sw128(smem_u32(sKV), 16, 1024);
+    const uint64_t v_desc0 = make_smem_desc_sw128(smem_u32(sKV), kA4BN * 128, 1024);
+    mbar_wait(q_full, 0);
+    int remaining = 2 * (n_tiles[0] + n_tiles[1]);
+    uint32_t idle = 0;
+    while (remaining > 0) {
+      bool progressed = false;
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        if (next_qk[q] == next_pv[q] && next_qk[q] < n_tiles[q]) {
+          // ---- S[q] = Q_q . K_j^T   (P.V of tile j-1 was issued before: it has read P out of these columns)
+          const int j = next_qk[q];
+          const int i = j == 0 ? 0 : 2 * j - 1, st = i % Cfg::kStages;      // ring position of K_j
+          const uint32_t ph = (i / Cfg::kStages) & 1;
+          if (mbar_test_wait(&kv_full[st], ph)) {
+            tc_fence_after();
+            if (elect_one()) {
+              const uint64_t qd = desc_advance(q_desc0, q * Cfg::kQBytes);
+              const uint64_t kd = desc_advance(k_desc0, st * Cfg::kKVBytes);
+              const uint32_t s_tmem = tmem_base + Cfg::kSCol + q * 128;
+              mma_bf16_ss_c<false>(s_tmem, qd, kd, idesc_qk);
+#pragma unroll
+              for (int kk = 1; kk < D / 16; ++kk) {
+                const uint32_t o = (kk >> 2) * (kA4BM * 128) + (kk & 3) * 32;
+                mma_bf16_ss_c<true>(s_tmem, desc_advance(qd, o), desc_advance(kd, o), idesc_qk);
+              }
+              mma_commit(&s_full[q]);
+              mma_commit(&kv_empty[st]);
+              if (j >= n_tiles[q ^ 1]) mbar_arrive(&kv_empty[st]);   // the other tile never reads K_j
+            }
+            __syncwarp();
+            ++next_qk[q];
+            --remaining;
+            progressed = true;
+          }
+        } else if (next_pv[q] < next_qk[q]) {
+          // ---- O[q] += P_q . V_j, P read from TMEM
+          const int j = next_pv[q];
+          const int i = (j + 1 < n_max) ? 2 * j + 2 : 2 * j + 1, st = i % Cfg::kStages;   // ring position of V_j
+          const uint32_t ph = (i / Cfg::kStages) & 1;
+          if (mbar_test_wait(&p_full[q], j & 1) && mbar_test_wait(&kv_full[st], ph)) {
+            tc_fence_after();
+            if (elect_one()) {
+              const uint64_t vd = desc_advance(v_desc0, st * Cfg::kKVBytes);
+              const uint32_t p_tmem = tmem_base + Cfg::kSCol + q * 128;     // 16 keys = 8 columns per MMA
+              const uint32_t o_tmem = tmem_base + Cfg::kOCol + q * 128;
+              if (j == 0) mma_bf16_ts_c<false>(o_tmem, p_tmem, vd, idesc_pv);
+              else mma_bf16_ts_c<true>(o_tmem, p_tmem, vd, idesc_pv);
+#pragma unroll
+              for (int kk = 1; kk < kA4BN / 16; ++kk)
+                mma_bf16_ts_c<true>(o_tmem, p_tmem + kk * 8, desc_advance(vd, kk * (16 * 128)), idesc_pv);
+              if (j == n_tiles[q] - 1) mma_commit(&o_done[q]);
+              mma_commit(&kv_empty[st]);
+              if (j >= n_tiles[q ^ 1]) mbar_arrive(&kv_empty[st]);
+            }
+            __syncwarp();
+            ++next_pv[q];
+            --remaining;
+            progressed = true;
+          }
+        }
+      }
+#if B200_WATCHDOG
+      if (progressed) {
+        idle = 0;
+      } else if (++idle > (1u << 26)) {
+        if (lane == 0)
+          printf("b200: attention4 MMA scheduler stuck block=(%d,%d,%d) qk=(%d,%d) pv=(%d,%d)\n", (int)blockIdx.x,
+                 (int)blockIdx.y, (int)blockIdx.z, next_qk[0], next_qk[1], next_pv[0], next_pv[1]);
+        __trap();
+      }
+#endif
+    }
+  }
+  } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");
+    // ===================== softmax / correction / epilogue =====================
+    const int q = (warp - 4) >> 2;               // query tile of this warp group
+    const int quad = warp & 3;                   // TMEM lane quadrant
+    const int row = quad * 32 + lane;
+    const int f = f_base + q * kA4BM + row;
+    const int nt = n_tiles[q];
+    const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
+    const uint32_t s_tmem = lane_base + Cfg::kSCol + q * 128;
+    const uint32_t o_tmem = lane_base + Cfg::kOCol + q * 128;
+    float m_used = -INFINITY;
+    float l_sum = 0.f;
+    for (int j = 0; j < nt; ++j) {
+      const int t0 = j * kA4BN;
+      int limit = p.Sk - t0;
+      if (p.causal) limit = min(limit, f + off + 1 - t0);
+      const bool need_mask = limit < kA4BN;
+      mbar_wait(&s_full[q], j & 1);
+      tc_fence_after();
+      // whole score row -> registers, then S[q] is free for Q.K^T of the next KV tile
+      uint32_t s[128];
+      {
+        uint32_t(&s0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[0]);
+        uint32_t(&s1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[32]);
+        uint32_t(&s2)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[64]);
+        uint32_t(&s3)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[96]);
+        tmem_ld_32x32(s_tmem, s0);
+        tmem_ld_32x32(s_tmem + 32, s1);
+        tmem_ld_32x32(s_tmem + 64, s2);
+        tmem_ld_32x32(s_tmem + 96, s3);
+        tmem_wait_ld();
+      }
+      if (__any_sync(0xffffffffu, need_mask)) {     // warp-uniform: only diagonal / tail tiles pay for masking
+        asm volatile("" ::: "memory");               // keep this a branch (not 128 predicated selects on every tile)
+#pragma unroll
+        for (int i = 0; i < 128; ++i)
+          if (i >= limit) s[i] = 0xff800000u;        // -inf
+      }
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};   // four chains instead of one 64-deep one
+#pragma unroll
+      for (int i = 0; i < 128; i += 8) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          mx4[c] = max3g(mx4[c], __uint_as_float(s[i + 2 * c]), __uint_as_float(s[i + 2 * c + 1]));
+      }
+      const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+      const float m_tile = mx * p.scale_log2;
+      float factor = 1.0f;
+      bool rescale = false;
+      if (j == 0) {
+        m_used = m_tile;
+      } else if (m_tile > m_used + kA4Rescale) {
+        factor = exp2_approx(m_used - m_tile);
+        m_used = m_tile;
+        rescale = true;
+      }
+      // S(j) complete implies P.V(j-1) complete (same issuing thread, in order): O[q] is stable here
+      if (__any_sync(0xffffffffu, rescale)) {
+        l_sum *= factor;
+#pragma unroll 1
+        for (int c = 0; c < D / 32; ++c) {
+          uint32_t r[32];
+          tmem_ld_32x32(o_tmem + c * 32, r);
+          tmem_wait_ld();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * factor);
+          tmem_st_32x32(o_tmem + c * 32, r);
+        }
+        tmem_wait_st();
+      }
+      // p = exp2(s * scale_log2 - m_used): packed f32x2 FMA / ADD, one MUFU per element; the bf16 pairs
+      // overwrite s[] in place (pair i -> s[i]) and go back to TMEM columns [0, 64) of this S tile
+      const uint64_t scale2 = pack_f32x2(p.scale_log2, p.scale_log2);
+      const uint64_t negm2 = pack_f32x2(-m_used, -m_used);
+      uint64_t sum2[2] = {0ull, 0ull};
+#pragma unroll
+      for (int i = 0; i < 64; ++i) {
+        const uint64_t x2 = fma_f32x2(pack_f32x2(__uint_as_float(s[2 * i]), __uint_as_float(s[2 * i + 1])), scale2, negm2);
+        float x0, x1;
+        unpack_f32x2(x2, x0, x1);
+        const float p0 = exp2_approx(x0), p1 = exp2_approx(x1);
+        sum2[i & 1] = add_f32x2(sum2[i & 1], pack_f32x2(p0, p1));
+        s[i] = pack_bf16x2(p0, p1);          // keys (2i, 2i+1): low half = even key
+      }
+      {
+        float a0, a1, b0, b1;
+        unpack_f32x2(sum2[0], a0, a1);
+        unpack_f32x2(sum2[1], b0, b1);
+        l_sum += (a0 + a1) + (b0 + b1);
+      }
+      {
+        const uint32_t(&p0)[32] = *reinterpret_cast<const uint32_t(*)[32]>(&s[0]);
+        const uint32_t(&p1)[32] = *reinterpret_cast<const uint32_t(*)[32]>(&s[32]);
+        tmem_st_32x32(s_tmem, p0);
+        tmem_st_32x32(s_tmem + 32, p1);
+        tmem_wait_st();
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&p_full[q]);
+    }
+    if (nt > 0) {
+      mbar_wait(&o_done[q], 0);
+      tc_fence_after();
+      const float inv_l = 1.0f / l_sum;
+      __nv_bfloat16* dst = p.O + batch * p.o_stride_b + static_cast<int64_t>(f) * p.o_stride_s + head * p.o_stride_h;
+#pragma unroll 1
+      for (int c = 0; c < D / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(o_tmem + c * 32, r);
+        tmem_wait_ld();
+        if (f < p.Sq) {
+#pragma unroll
+          for (int i = 0; i < 32; i += 8) {
+            uint4 o;
+            o.x = pack_bf16x2(__uint_as_float(r[i]) * inv_l, __uint_as_float(r[i + 1]) * inv_l);
+            o.y = pack_bf16x2(__uint_as_float(r[i + 2]) * inv_l, __uint_as_float(r[i + 3]) * inv_l);
+            o.z = pack_bf16x2(__uint_as_float(r[i + 4]) * inv_l, __uint_as_float(r[i + 5]) * inv_l);
+            o.w = pack_bf16x2(__uint_as_float(r[i + 6]) * inv_l, __uint_as_float(r[i + 7]) * inv_l);
+            *reinterpret_cast<uint4*>(dst + c * 32 + i) = o;
+          }
+        }
+      }
+    }
+  }
+
+  __syncwarp();
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+  }
+}
+
+int make_bsnh_map(CUtensorMap* tm, const void* base, int B, int S, int H, int D, int64_t sb, int64_t ss, int64_t sh,
+                  int rows);
+
+template <int D>
+static int launch_attention4(const void* Q, const void* K, const void* V, const Attn4Params& p, int B, int Sq, int Sk,
+                             int H, const int64_t* qs, const int64_t* ks, const int64_t* vs, cudaStream_t stream) {
+  using Cfg = Attn4Cfg<D>;
+  static_assert(Cfg::kStages >= 3, "KV ring needs at least three stages");
+  static_assert(kA4BN == 128, "P occupies 64 TMEM columns");
+  CUtensorMap tmQ, tmK, tmV;
+  int rc = make_bsnh_map(&tmQ, Q, B, Sq, H, D, qs[0], qs[1], qs[2], kA4BM);
+  if (rc != B200_OK) return rc;
+  rc = make_bsnh_map(&tmK, K, B, Sk, H, D, ks[0], ks[1], ks[2], kA4BN);
+  if (rc != B200_OK) return rc;
+  rc = make_bsnh_map(&tmV, V, B, Sk, H, D, vs[0], vs[1], vs[2], kA4BN);
+  if (rc != B200_OK) return rc;
+  auto kern = attention_fwd4_kernel<D>;
+  B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+  dim3 grid(p.num_q_blocks, H, B);
+  kern<<<grid, kA4Threads, Cfg::kSmemBytes, stream>>>(tmQ, tmK, tmV, p);
+  B200_CUDA_CHECK(cudaGetLastError());
+  launch_counter().fetch_add(1);
+  return B200_OK;
+}
+
+int attention_fwd4_dispatch(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
+                            const int64_t* strides, float scale, int causal, cudaStream_t stream) {
+  Attn4Params p = {};
+  p.O = reinterpret_cast<__nv_bfloat16*>(O);
+  p.Sq = Sq;
+  p.Sk = Sk;
+  p.o_stride_b = strides[9];
+  p.o_stride_s = strides[10];
+  p.o_stride_h = strides[11];
+  p.scale_log2 = scale * 1.4426950408889634f;
+  p.causal = causal ? 1 : 0;
+  p.num_q_blocks = (Sq + 2 * kA4BM - 1) / (2 * kA4BM);
+  if (D == 64) return launch_attention4<64>(Q, K, V, p, B, Sq, Sk, H, strides, strides + 3, strides + 6, stream);
+  return launch_attention4<128>(Q, K, V, p, B, Sq, Sk, H, strides, strides + 3, strides + 6, stream);
+}
+
+}  // namespace b200

@@ -101,7 +101,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint64_t* tmem_empty_bar = tmem_full_bar + Cfg::kAccStages;
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty_bar + Cfg::kAccStages);
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = uniform_warp_idx();
   const int lane = threadIdx.x & 31;
   uint32_t cta_rank = 0;
   if (G == 2) asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta_rank));
@@ -140,8 +140,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
 
-  if (warp == 0 && lane == 0) {
-    // ===================== TMA producer =====================
+  if (warp == 0) {
+    // ===================== TMA producer (whole warp in the loop, one elected lane issues) =====================
     int stage = 0;
     uint32_t phase = 0;
     for (int tile = worker; tile < num_tiles; tile += num_workers) {
@@ -158,6 +158,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         uint8_t* sa = smem + stage * Cfg::kStageBytes;
         uint8_t* sb = sa + Cfg::kABytes;
         const int k0 = kb * kBK;
+        if (elect_one()) {
         if (G == 1) {
           mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
           tma_load_2d(sa, &tmA, &full_bar[stage], k0, m0);
@@ -180,12 +181,23 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               tma_load_2d_cg2(sb + c * (kBK * 128), &tmB, &full_bar[stage], n0 + c * 64, k0);
           }
         }
+        }
+        __syncwarp();
         if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
       }
     }
-  } else if (warp == 1 && lane == 0 && leader) {
+  } else if (warp == 1 && leader) {
     // ===================== MMA issuer (leader CTA only) =====================
     constexpr uint32_t idesc = make_idesc_bf16(kBM * G, BN, false, !kBKmajor);
+    // Descriptors of stage 0, built once; per MMA only a constant is added (the issuing thread has 128 cycles
+    // per MMA at most -- rebuilding two 64-bit descriptors each time cost ~20 % of the tensor pipe).
+    //   A: K-major, 32 bytes of K per MMA inside the 128-byte swizzle row.
+    //   B K-major: same.  B MN-major ([K,N] row-major): 16 K-rows of 128 B per MMA, 64-column chunks kBK*128 B apart.
+    const uint64_t a_desc0 = make_smem_desc_sw128(smem_u32(smem), 16, 1024);
+    const uint64_t b_desc0 = kBKmajor ? make_smem_desc_sw128(smem_u32(smem) + Cfg::kABytes, 16, 1024)
+                                      : make_smem_desc_sw128(smem_u32(smem) + Cfg::kABytes, kBK * 128, 1024);
+    constexpr uint32_t kAStep = kUmmaK * 2;
+    constexpr uint32_t kBStep = kBKmajor ? kUmmaK * 2 : kUmmaK * 128;
     int stage = 0;
     uint32_t phase = 0;
     int acc = 0;
@@ -197,27 +209,28 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       for (int kb = 0; kb < num_kb; ++kb) {
         mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
-        const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
-        const uint32_t sb = sa + Cfg::kABytes;
+        const uint64_t da = desc_advance(a_desc0, stage * Cfg::kStageBytes);
+        const uint64_t db = desc_advance(b_desc0, stage * Cfg::kStageBytes);
+        if (elect_one()) {
+        if (G == 1) {
+          if (kb == 0) mma_bf16_ss_c<false>(tmem_d, da, db, idesc);
+          else mma_bf16_ss_c<true>(tmem_d, da, db, idesc);
 #pragma unroll
-        for (int k = 0; k < kBK / kUmmaK; ++k) {
-          // A: K-major, 32 bytes of K per MMA inside the 128-byte swizzle row
-          const uint64_t da = make_smem_desc_sw128(sa + k * (kUmmaK * 2), 16, 1024);
-          // B K-major: same; B MN-major ([K,N] row-major): 16 K-rows of 128 B per MMA,
-          // 64-column chunks kBK*128 bytes apart
-          const uint64_t db = kBKmajor ? make_smem_desc_sw128(sb + k * (kUmmaK * 2), 16, 1024)
-                                       : make_smem_desc_sw128(sb + k * (kUmmaK * 128), kBK * 128, 1024);
-          const uint32_t accum = (kb > 0 || k > 0) ? 1u : 0u;
-          if (G == 1) mma_bf16_ss(tmem_d, da, db, idesc, accum);
-          else mma_bf16_ss_cg2(tmem_d, da, db, idesc, accum);
+          for (int k = 1; k < kBK / kUmmaK; ++k)
+            mma_bf16_ss_c<true>(tmem_d, desc_advance(da, k * kAStep), desc_advance(db, k * kBStep), idesc);
+          mma_commit(&empty_bar[stage]);          // frees this smem stage once the MMAs above have read it
+          if (kb == num_kb - 1) mma_commit(&tmem_full_bar[acc]);
+        } else {
+          if (kb == 0) mma_bf16_ss_cg2_c<false>(tmem_d, da, db, idesc);
+          else mma_bf16_ss_cg2_c<true>(tmem_d, da, db, idesc);
+#pragma unroll
+          for (int k = 1; k < kBK / kUmmaK; ++k)
+            mma_bf16_ss_cg2_c<true>(tmem_d, desc_advance(da, k * kAStep), desc_advance(db, k * kBStep), idesc);
+          mma_commit_cg2(&empty_bar[stage], 0x3);  // ... in both CTAs of the pair
+          if (kb == num_kb - 1) mma_commit_cg2(&tmem_full_bar[acc], 0x3);
         }
-        // frees this smem stage (in both CTAs) once the MMAs above have read it
-        if (G == 1) mma_commit(&empty_bar[stage]);
-        else mma_commit_cg2(&empty_bar[stage], 0x3);
-        if (kb == num_kb - 1) {
-          if (G == 1) mma_commit(&tmem_full_bar[acc]);
-          else mma_commit_cg2(&tmem_full_bar[acc], 0x3);
         }
+        __syncwarp();
         if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
       }
       if (++acc == Cfg::kAccStages) { acc = 0; acc_phase ^= 1; }

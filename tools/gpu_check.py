@@ -131,6 +131,8 @@ def main():
             print(f"  f32 B={Bt} M={M} N={N} K={K}: max_rel={err:.3e} {'OK' if good else 'FAIL'}", flush=True)
             ok &= good
     elif args.what == "attn":
+        if args.g:
+            capi.set_attention_variant(args.g)
         sys.path.insert(0, ROOT)
         from oracle import reference_math as rm
         for (B, Sq, Sk, H, D, causal) in [(1, 128, 128, 1, 64, False), (1, 128, 128, 1, 128, False),
@@ -227,6 +229,8 @@ def main():
             capi.attention_fwd(q, k, v)
         torch.cuda.synchronize()
     elif args.what == "attn_time":
+        if args.g:
+            capi.set_attention_variant(args.g)
         for (B, S, H, D, causal) in [(8, 4096, 32, 128, False), (8, 4096, 32, 128, True), (4, 8192, 32, 128, True),
                                      (8, 4096, 32, 64, False)]:
             q, k, v = (torch.randn(B, S, H, D, device="cuda").to(torch.bfloat16) for _ in range(3))
