@@ -351,6 +351,13 @@ static int g_attn_variant = 0;
 
 using namespace b200;
 
+namespace b200 { extern long long* g_attn_prof; }
+// bring-up aid: device buffer of >= 8 int64 receiving per-phase cycle totals of one softmax warp (NULL = off)
+extern "C" int b200_attention_set_profile_buffer(void* dev_buf) {
+  b200::g_attn_prof = reinterpret_cast<long long*>(dev_buf);
+  return B200_OK;
+}
+
 extern "C" int b200_attention_set_variant(int variant) {
   if (variant < 0 || variant > 4) return fail(B200_ERR_INVALID_ARGUMENT, "attention variant must be 0..4");
   g_attn_variant = variant;

@@ -44,6 +44,7 @@ struct Attn2Params {
   float scale_log2;
   int causal;
   int num_q_blocks;
+  long long* prof;   // optional: per-phase cycle totals of block (0,0,0), softmax warp 4 / MMA warp (bring-up aid)
 };
 
 __device__ __forceinline__ float max3(float a, float b, float c) {
@@ -246,6 +247,10 @@ attention_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     uint8_t* sPq = sP + q * Cfg::kPBytes;
     float m_used = -INFINITY;
     float l_sum = 0.f;
+    const bool prof = p.prof != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && warp == 4 && lane == 0;
+    long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    long long tp = clock64();
+#define PROF_MARK(k) do { if (prof) { long long _t = clock64(); tacc[k] += _t - tp; tp = _t; } } while (0)
     for (int j = 0; j < nt; ++j) {
       const int t0 = j * kA2BN;
       int limit = p.Sk - t0;
@@ -253,6 +258,7 @@ attention_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
       const bool need_mask = limit < kA2BN;
       mbar_wait(&s_full[q], j & 1);
       tc_fence_after();
+      PROF_MARK(0);
       // whole score row -> registers, then S[q] is free for Q.K^T of the next KV tile
       uint32_t s[128];
       {
@@ -266,6 +272,7 @@ attention_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         tmem_ld_32x32(s_tmem + 96, s3);
         tmem_wait_ld();
       }
+      PROF_MARK(1);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&s_free[q]);
@@ -293,11 +300,13 @@ attention_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         m_used = m_tile;
         rescale = true;
       }
+      PROF_MARK(2);
       // P[q] buffer is free and O[q] is stable once P.V of tile j-1 has completed
       if (j > 0) {
         mbar_wait(&pv_done[q], (j - 1) & 1);
         tc_fence_after();
       }
+      PROF_MARK(3);
       if (__any_sync(0xffffffffu, rescale)) {
         l_sum *= factor;
 #pragma unroll 1
@@ -339,10 +348,16 @@ attention_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         unpack_f32x2(sum2[1], b0, b1);
         l_sum += (a0 + a1) + (b0 + b1);
       }
+      PROF_MARK(4);
       fence_async_smem();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&p_full[q]);
+      PROF_MARK(5);
+    }
+    if (prof) {
+      for (int k = 0; k < 6; ++k) p.prof[k] = tacc[k];
+      p.prof[6] = nt;
     }
     if (nt > 0) {
       mbar_wait(&pv_done[q], (nt - 1) & 1);
@@ -402,6 +417,8 @@ static int launch_attention2(const void* Q, const void* K, const void* V, const 
   return B200_OK;
 }
 
+long long* g_attn_prof = nullptr;
+
 int attention_fwd2_dispatch(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
                             const int64_t* strides, float scale, int causal, cudaStream_t stream) {
   Attn2Params p = {};
@@ -414,6 +431,7 @@ int attention_fwd2_dispatch(const void* Q, const void* K, const void* V, void* O
   p.scale_log2 = scale * 1.4426950408889634f;
   p.causal = causal ? 1 : 0;
   p.num_q_blocks = (Sq + 2 * kA2BM - 1) / (2 * kA2BM);
+  p.prof = g_attn_prof;
   if (D == 64) return launch_attention2<64>(Q, K, V, p, B, Sq, Sk, H, strides, strides + 3, strides + 6, stream);
   return launch_attention2<128>(Q, K, V, p, B, Sq, Sk, H, strides, strides + 3, strides + 6, stream);
 }

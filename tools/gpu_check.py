@@ -223,6 +223,28 @@ def main():
                 print(f"  {name:36s} M={M} N={N} K={K}: {ms:.3f} ms {2 * M * N * K / ms / 1e9:.1f} TFLOP/s", flush=True)
             lib.b200_gemm_set_max_stages(0)
             capi.set_gemm_group_m(0)
+    elif args.what == "attn_phases":
+        import ctypes
+        lib = capi.load()
+        lib.b200_attention_set_profile_buffer.argtypes = [ctypes.c_void_p]
+        capi.set_attention_variant(2)
+        buf = torch.zeros(8, dtype=torch.int64, device="cuda")
+        B, S, H, D = 8, 4096, 32, 128
+        q, k, v = (torch.randn(B, S, H, D, device="cuda").to(torch.bfloat16) for _ in range(3))
+        o = torch.empty_like(q)
+        for _ in range(2):
+            capi.attention_fwd(q, k, v, out=o)
+        lib.b200_attention_set_profile_buffer(ctypes.c_void_p(buf.data_ptr()))
+        capi.attention_fwd(q, k, v, out=o)
+        torch.cuda.synchronize()
+        lib.b200_attention_set_profile_buffer(None)
+        t = buf.cpu().tolist()
+        nt = max(t[6], 1)
+        names = ["wait s_full", "tmem ld S", "mask+max+decide", "wait pv_done", "exp + P store", "fence + arrive"]
+        print(f"  softmax warp 4 of block (0,0,0): {nt} KV tiles, cycles per tile:")
+        for n, c in zip(names, t[:6]):
+            print(f"    {n:18s} {c / nt:8.0f}")
+        print(f"    {'total':18s} {sum(t[:6]) / nt:8.0f}", flush=True)
     elif args.what == "attn_prof":
         q, k, v = (torch.randn(2, 4096, 16, 128, device="cuda").to(torch.bfloat16) for _ in range(3))
         for _ in range(3):
