@@ -392,7 +392,17 @@ static int launch_gemm(const void* A, int64_t lda, const void* B, int64_t ldb, c
   if (G == 2 && stages > 4) stages = 4;
   if (g_max_stages > 0 && g_max_stages < stages) stages = g_max_stages;
   p.num_stages = stages;
-  p.group_m = g_group_m > 0 ? g_group_m : 8;   // raster group: flat within noise at 4 stages (r01_gemm_sweep2.log)
+  if (g_group_m > 0) {
+    p.group_m = g_group_m;
+  } else {
+    // Raster group = the A row-panels (group_m x 128*G rows x K) that stay L2-resident (~64 MB of the 126 MB)
+    // while the B panels stream past once per group.  ncu: at group 8 the K=4096 FFN GEMM re-read B eight
+    // times (1.23 GB read vs 0.27 GB algorithmic, profiles/r01_ncu_gemm_full_summary_v2.txt); speed is flat
+    // within noise (r01_gemm_sweep2.log), the DRAM bytes are what this saves.
+    const int64_t panel_bytes = static_cast<int64_t>(kBM) * G * p.K * 2;
+    const int64_t gm = (64ll << 20) / (panel_bytes > 0 ? panel_bytes : 1);
+    p.group_m = static_cast<int>(gm < 4 ? 4 : (gm > 32 ? 32 : gm));
+  }
   CUtensorMap tmA, tmB;
   {
     uint64_t a_rows = static_cast<uint64_t>(p.M);

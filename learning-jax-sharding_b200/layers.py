@@ -478,7 +478,8 @@ class FFNBench:
         return self.layer.forward(self.x, record=self._record if record_kernels else None)
 
     def mean_kernel_ms(self):
-        """Mean device time of one GEMM launch, from events recorded around every launch of the timed region."""
+        """(mean device time of one GEMM launch, number of GEMM launches timed), from events recorded around
+        every GEMM launch of the timed region."""
         total, n = 0.0, 0
         prev = None
         for tag, ev in self._events:
@@ -486,7 +487,7 @@ class FFNBench:
                 total += prev.elapsed_time(ev)
                 n += 1
             prev = ev
-        return total / max(n, 1)
+        return total / max(n, 1), n
 
     # --- end-to-end step: host x -> device -> FFN -> host y
     def step_e2e(self):
