@@ -402,9 +402,11 @@ class FFNBench:
         self.T, self.d, self.f = T, d, f
         self.mode = cfg.get("parallelism", "tp") if world > 1 else "single"
         group = None
+        self._dist = None
         if world > 1:
             import torch.distributed as dist
             group = dist.group.WORLD
+            self._dist = dist
         x = _synthetic((T, d), 0, "activation").to(torch.bfloat16)
         w1 = _synthetic((d, f), 1, "weight").to(torch.bfloat16)
         b1 = _synthetic((f,), 2, "bias").to(torch.bfloat16)
@@ -497,9 +499,19 @@ class FFNBench:
         main = torch.cuda.current_stream(self.dev)
         if self.world > 1:
             self.copy_in.wait_stream(main)
-            with torch.cuda.stream(self.copy_in):
-                self.x_stage.copy_(self.x_host, non_blocking=True)
-            main.wait_stream(self.copy_in)
+            if self.mode == "tp":
+                # x is replicated over the model axis: every rank uploads only ITS 1/W of the rows over PCIe
+                # and the ranks all-gather the rest over NVLink (8 x 134 MB of host reads would be PCIe-bound)
+                rows = self.T // self.world
+                sl = slice(self.rank * rows, (self.rank + 1) * rows)
+                with torch.cuda.stream(self.copy_in):
+                    self.x_stage[sl].copy_(self.x_host[sl], non_blocking=True)
+                main.wait_stream(self.copy_in)
+                self._dist.all_gather_into_tensor(self.x_stage, self.x_stage[sl])
+            else:
+                with torch.cuda.stream(self.copy_in):
+                    self.x_stage.copy_(self.x_host, non_blocking=True)
+                main.wait_stream(self.copy_in)
             y = self.layer.forward(self.x_stage)
             self.copy_out.wait_stream(main)
             with torch.cuda.stream(self.copy_out):
@@ -527,7 +539,10 @@ class FFNBench:
         return self.y_host
 
     def e2e_bytes(self):
-        return self.x_host.numel() * 2, self.y_host.numel() * 2
+        h2d = self.x_host.numel() * 2
+        if self.world > 1 and self.mode == "tp":
+            h2d //= self.world          # each rank uploads its share of the replicated x
+        return h2d, self.y_host.numel() * 2
 
     def ncu_traffic_bytes(self):
         """dram read+write bytes per GEMM launch from the committed ncu --set full capture, if any."""
