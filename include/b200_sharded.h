@@ -223,6 +223,12 @@ int b200_peer_free(void* dev_ptr);
  * read-only, so pulling needs no cross-rank synchronisation. */
 int b200_peer_copy2d(void* dst, int64_t dst_pitch_bytes, const void* src, int64_t src_pitch_bytes, int64_t width_bytes,
                      int64_t rows, void* stream);
+/* The same pull as ONE kernel: column chunk [src_off_bytes, +width_bytes) of every rank's [rows, src_pitch] shard
+ * (src_bases_dev: DEVICE array of `world` base pointers, own shard included) into rows p*rows.. of dst.  16-byte
+ * loads from peer HBM over NVLink, eight in flight per thread, `ctas` CTAs of 256 threads that co-reside with
+ * the persistent GEMM.  Reaches NVLink bandwidth where strided copy-engine copies do not. */
+int b200_peer_gather(void* const* src_bases_dev, int world, int rank, int64_t src_off_bytes, int64_t src_pitch_bytes,
+                     void* dst, int64_t dst_pitch_bytes, int rows, int64_t width_bytes, int ctas, void* stream);
 int b200_peer_barrier(void* const* flag_ptrs_dev, int rank, int world, uint32_t epoch, void* stream);
 int b200_sum_bf16_partials(const void* src, int64_t src_stride, int nsrc, const void* bias, int64_t cols, void* dst,
                            int64_t n, void* stream);

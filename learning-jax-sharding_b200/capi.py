@@ -41,6 +41,7 @@ EXPORTED_SYMBOLS = (
     "b200_peer_close",
     "b200_peer_free",
     "b200_peer_copy2d",
+    "b200_peer_gather",
     "b200_peer_barrier",
     "b200_sum_bf16_partials",
 )
@@ -86,6 +87,7 @@ def load():
     lib.b200_peer_close.argtypes = [vp]
     lib.b200_peer_free.argtypes = [vp]
     lib.b200_peer_copy2d.argtypes = [vp, i64, vp, i64, i64, i64, vp]
+    lib.b200_peer_gather.argtypes = [vp, i32, i32, i64, i64, vp, i64, i32, i64, i32, vp]
     lib.b200_peer_barrier.argtypes = [vp, i32, i32, ctypes.c_uint32, vp]
     lib.b200_sum_bf16_partials.argtypes = [vp, i64, i32, vp, i64, vp, i64, vp]
     lib.b200_gemm_f32.argtypes = [vp, i64, i64, vp, i64, i64, vp, i64, i64, i32, i32, i32, i32, i32, vp]
@@ -346,3 +348,11 @@ def peer_copy2d(dst_ptr: int, dst_pitch: int, src_ptr: int, src_pitch: int, widt
     rc = load().b200_peer_copy2d(ctypes.c_void_p(dst_ptr), dst_pitch, ctypes.c_void_p(src_ptr), src_pitch, width_bytes,
                                  rows, ctypes.c_void_p(stream.cuda_stream))
     _check(rc, "b200_peer_copy2d")
+
+
+def peer_gather(src_bases, world: int, rank: int, src_off: int, src_pitch: int, dst_ptr: int, dst_pitch: int, rows: int,
+                width_bytes: int, ctas: int, stream):
+    """One-kernel pull of a column chunk of every rank's shard (src_bases: CUDA int64 tensor of base pointers)."""
+    rc = load().b200_peer_gather(_ptr(src_bases), world, rank, src_off, src_pitch, ctypes.c_void_p(dst_ptr), dst_pitch,
+                                 rows, width_bytes, ctas, ctypes.c_void_p(stream.cuda_stream))
+    _check(rc, "b200_peer_gather")

@@ -75,9 +75,63 @@ __global__ void __launch_bounds__(256) sum_bf16_partials_kernel(const __nv_bfloa
   }
 }
 
+// Pull one column chunk of every rank's weight shard into the local gathered matrix: W shards of
+// [rows, src_pitch] (this rank's own included), destination rows p*rows .. (p+1)*rows of a [W*rows, dst_pitch]
+// matrix.  16-byte loads straight from the peers' HBM over NVLink, eight in flight per thread; each CTA starts
+// at a different peer so that all links are busy at once.
+__global__ void __launch_bounds__(256) peer_gather_kernel(const uint8_t* const* __restrict__ src_bases, int world,
+                                                         int rank, int64_t src_off_bytes, int64_t src_pitch,
+                                                         uint8_t* __restrict__ dst, int64_t dst_pitch, int rows,
+                                                         int width16) {
+  const int64_t units = static_cast<int64_t>(rows) * width16;            // 16-byte units of one shard's chunk
+  const int64_t per_cta = (units + gridDim.x - 1) / gridDim.x;
+  const int64_t u_begin = per_cta * blockIdx.x;
+  const int64_t u_end = u_begin + per_cta < units ? u_begin + per_cta : units;
+  for (int pp = 0; pp < world; ++pp) {
+    const int p = (rank + 1 + pp + blockIdx.x) % world;
+    const uint8_t* src = src_bases[p] + src_off_bytes;
+    uint8_t* out = dst + static_cast<int64_t>(p) * rows * dst_pitch;
+    for (int64_t u0 = u_begin + threadIdx.x; u0 < u_end; u0 += 8 * 256) {
+      uint4 v[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int64_t u = u0 + k * 256;
+        if (u < u_end) {
+          const int64_t r = u / width16, c = u % width16;
+          v[k] = *reinterpret_cast<const uint4*>(src + r * src_pitch + c * 16);
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int64_t u = u0 + k * 256;
+        if (u < u_end) {
+          const int64_t r = u / width16, c = u % width16;
+          *reinterpret_cast<uint4*>(out + r * dst_pitch + c * 16) = v[k];
+        }
+      }
+    }
+  }
+}
+
 }  // namespace b200
 
 using namespace b200;
+
+extern "C" int b200_peer_gather(void* const* src_bases_dev, int world, int rank, int64_t src_off_bytes,
+                                int64_t src_pitch_bytes, void* dst, int64_t dst_pitch_bytes, int rows,
+                                int64_t width_bytes, int ctas, void* stream) {
+  B200_REQUIRE(src_bases_dev && dst && world >= 1 && rank >= 0 && rank < world && rows > 0 && width_bytes > 0,
+               "b200_peer_gather: bad arguments");
+  B200_REQUIRE(width_bytes % 16 == 0 && src_pitch_bytes % 16 == 0 && dst_pitch_bytes % 16 == 0 && src_off_bytes % 16 == 0,
+               "b200_peer_gather: offsets, pitches and width must be multiples of 16 bytes");
+  B200_REQUIRE(ctas >= 1 && ctas <= 1024, "b200_peer_gather: ctas must be in [1, 1024]");
+  peer_gather_kernel<<<ctas, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const uint8_t* const*>(src_bases_dev), world, rank, src_off_bytes, src_pitch_bytes,
+      reinterpret_cast<uint8_t*>(dst), dst_pitch_bytes, rows, static_cast<int>(width_bytes / 16));
+  B200_CUDA_CHECK(cudaGetLastError());
+  launch_counter().fetch_add(1);
+  return B200_OK;
+}
 
 extern "C" int b200_peer_alloc(uint64_t bytes, void** dev_ptr, void* handle64) {
   B200_REQUIRE(bytes > 0 && dev_ptr && handle64, "b200_peer_alloc: bad arguments");

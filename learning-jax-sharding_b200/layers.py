@@ -302,7 +302,8 @@ class PeerGatherFFN:
     column chunk at a time on side streams, while the GEMM of the previous chunk runs.  Pull order is
     staggered by rank so every source serves one reader at a time."""
 
-    def __init__(self, w1_shard, b1, w2_shard, b2, act: str, T_local: int, group, chunks: int = 4, copy_streams: int = 4):
+    def __init__(self, w1_shard, b1, w2_shard, b2, act: str, T_local: int, group, chunks: int = 4, copy_streams: int = 4,
+                 mode: str = "ce", ctas: int = 48):
         import torch.distributed as dist
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         W = self.world
@@ -325,6 +326,8 @@ class PeerGatherFFN:
         self.peer_base = [self.base if p == self.rank else capi.peer_open(bytes(handles[p].cpu().tolist()))
                           for p in range(W)]
         self.n1 = n1
+        self.mode, self.ctas = mode, ctas          # "kernel": b200_peer_gather (SM pull); "ce": copy-engine 2-D copies
+        self.src_bases = torch.tensor(self.peer_base, dtype=torch.int64, device=dev)
         self.w1g = torch.empty((self.k1 * W, self.F), dtype=torch.bfloat16, device=dev)
         self.w2g = torch.empty((self.k2 * W, self.d_model), dtype=torch.bfloat16, device=dev)
         self.h = torch.empty((T_local, self.F), dtype=torch.bfloat16, device=dev)
@@ -339,6 +342,13 @@ class PeerGatherFFN:
         rows, cols = (self.k1, self.F) if which == 0 else (self.k2, self.d_model)
         dst = self.w1g if which == 0 else self.w2g
         cw = cols // C
+        if self.mode == "kernel":
+            st = self.streams[0]
+            capi.peer_gather(self.src_bases, W, self.rank, (0 if which == 0 else self.n1) + j * cw * 2, cols * 2,
+                             dst.data_ptr() + j * cw * 2, cols * 2, rows, cw * 2, self.ctas, st)
+            for k, s_ in enumerate(self.streams):
+                self.ready[which * C + j][k].record(s_)
+            return
         for i in range(W):
             p = (self.rank + 1 + i) % W                       # own shard last
             st = self.streams[i % len(self.streams)]
@@ -418,10 +428,17 @@ class FFNBench:
             shard = (w1[rank * kl1:(rank + 1) * kl1].contiguous().to(dev), b1.to(dev),
                      w2[rank * kl2:(rank + 1) * kl2].contiguous().to(dev), b2.to(dev))
             self.layer = None
-            if os.environ.get("B200_FSDP_COLLECTIVE", "peer") == "peer":
+            # measured (profiles/r01_fsdp_gather_modes.md): copy-engine pulls win at 2 GPUs (2293 vs NCCL 2171
+            # TFLOP/s), NCCL all-gather wins at 8 (4182 vs 3615); the one-kernel SM pull is behind both
+            default_mode = "peer" if world <= 2 else "nccl"
+            fsdp_mode = os.environ.get("B200_FSDP_COLLECTIVE", default_mode)
+            if fsdp_mode in ("peer", "peer_kernel"):
                 try:
-                    self.layer = PeerGatherFFN(*shard, act, tl, group, chunks=chunks)
-                    self.collective = "copy-engine pulls of weight column chunks from peer HBM over NVLink, overlapped with GEMMs"
+                    self.layer = PeerGatherFFN(*shard, act, tl, group, chunks=chunks,
+                                               mode="kernel" if fsdp_mode == "peer_kernel" else "ce",
+                                               copy_streams=1 if fsdp_mode == "peer_kernel" else 4)
+                    self.collective = ("one-kernel SM pulls" if fsdp_mode == "peer_kernel" else "copy-engine pulls") + \
+                        " of weight column chunks from peer HBM over NVLink, overlapped with GEMMs"
                 except Exception as e:   # noqa: BLE001
                     if rank == 0:
                         print(f"[bench] peer gather unavailable ({e!r}); using NCCL", file=sys.stderr, flush=True)
