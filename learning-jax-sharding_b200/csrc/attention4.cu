@@ -48,6 +48,7 @@ struct Attn4Params {
   float scale_log2;
   int causal;
   int num_q_blocks;
+  long long* prof;   // optional: per-phase cycle totals of block (0,0,0), softmax warp 4 (bring-up aid)
 };
 
 __device__ __forceinline__ float max3g(float a, float b, float c) {
@@ -242,6 +243,10 @@ attention_fwd4_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     const uint32_t o_tmem = lane_base + Cfg::kOCol + q * 128;
     float m_used = -INFINITY;
     float l_sum = 0.f;
+    const bool prof = p.prof != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && warp == 4 && lane == 0;
+    long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    long long tp = clock64();
+#define PROF_MARK4(k) do { if (prof) { long long _t = clock64(); tacc[k] += _t - tp; tp = _t; } } while (0)
     for (int j = 0; j < nt; ++j) {
       const int t0 = j * kA4BN;
       int limit = p.Sk - t0;
@@ -249,6 +254,7 @@ attention_fwd4_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
       const bool need_mask = limit < kA4BN;
       mbar_wait(&s_full[q], j & 1);
       tc_fence_after();
+      PROF_MARK4(0);
       // whole score row -> registers, then S[q] is free for Q.K^T of the next KV tile
       uint32_t s[128];
       {
@@ -262,6 +268,7 @@ attention_fwd4_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         tmem_ld_32x32(s_tmem + 96, s3);
         tmem_wait_ld();
       }
+      PROF_MARK4(1);
       if (__any_sync(0xffffffffu, need_mask)) {     // warp-uniform: only diagonal / tail tiles pay for masking
         asm volatile("" ::: "memory");               // keep this a branch (not 128 predicated selects on every tile)
 #pragma unroll
@@ -286,6 +293,7 @@ attention_fwd4_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         m_used = m_tile;
         rescale = true;
       }
+      PROF_MARK4(2);
       // S(j) complete implies P.V(j-1) complete (same issuing thread, in order): O[q] is stable here
       if (__any_sync(0xffffffffu, rescale)) {
         l_sum *= factor;
@@ -300,6 +308,7 @@ attention_fwd4_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         }
         tmem_wait_st();
       }
+      PROF_MARK4(3);
       // p = exp2(s * scale_log2 - m_used): packed f32x2 FMA / ADD, one MUFU per element; the bf16 pairs
       // overwrite s[] in place (pair i -> s[i]) and go back to TMEM columns [0, 64) of this S tile
       const uint64_t scale2 = pack_f32x2(p.scale_log2, p.scale_log2);
@@ -320,6 +329,7 @@ attention_fwd4_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         unpack_f32x2(sum2[1], b0, b1);
         l_sum += (a0 + a1) + (b0 + b1);
       }
+      PROF_MARK4(4);
       {
         const uint32_t(&p0)[32] = *reinterpret_cast<const uint32_t(*)[32]>(&s[0]);
         const uint32_t(&p1)[32] = *reinterpret_cast<const uint32_t(*)[32]>(&s[32]);
@@ -330,6 +340,11 @@ attention_fwd4_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&p_full[q]);
+      PROF_MARK4(5);
+    }
+    if (prof) {
+      for (int k = 0; k < 6; ++k) p.prof[k] = tacc[k];
+      p.prof[6] = nt;
     }
     if (nt > 0) {
       mbar_wait(&o_done[q], 0);
@@ -390,6 +405,8 @@ static int launch_attention4(const void* Q, const void* K, const void* V, const 
   return B200_OK;
 }
 
+extern long long* g_attn_prof;
+
 int attention_fwd4_dispatch(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
                             const int64_t* strides, float scale, int causal, cudaStream_t stream) {
   Attn4Params p = {};
@@ -402,6 +419,7 @@ int attention_fwd4_dispatch(const void* Q, const void* K, const void* V, void* O
   p.scale_log2 = scale * 1.4426950408889634f;
   p.causal = causal ? 1 : 0;
   p.num_q_blocks = (Sq + 2 * kA4BM - 1) / (2 * kA4BM);
+  p.prof = g_attn_prof;
   if (D == 64) return launch_attention4<64>(Q, K, V, p, B, Sq, Sk, H, strides, strides + 3, strides + 6, stream);
   return launch_attention4<128>(Q, K, V, p, B, Sq, Sk, H, strides, strides + 3, strides + 6, stream);
 }

@@ -144,6 +144,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // ===================== TMA producer (whole warp in the loop, one elected lane issues) =====================
     int stage = 0;
     uint32_t phase = 0;
+    // A row-panels of the current raster group are re-read by every column block of the group: ask L2 to keep
+    // them (evict_last).  B keeps the default policy: its tiles are shared by the group_m CTAs that run next to
+    // each other, and evict_first made them miss (measured: DRAM reads 1.2 -> 3.4 GB, profiles/r01_l2_hint_experiment.md).
+    const uint64_t pol_a = l2_policy_evict_last();
     for (int tile = worker; tile < num_tiles; tile += num_workers) {
       int m_blk, n_blk;
       tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, m_blk, n_blk);
@@ -161,7 +165,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (elect_one()) {
         if (G == 1) {
           mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
-          tma_load_2d(sa, &tmA, &full_bar[stage], k0, m0);
+          tma_load_2d_hint(sa, &tmA, &full_bar[stage], k0, m0, pol_a);
           if (kBKmajor) {
             tma_load_2d(sb, &tmB, &full_bar[stage], k0, n0);
           } else {
@@ -172,7 +176,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         } else {
           // both CTAs' bytes complete on the leader's barrier
           if (leader) mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes * 2);
-          tma_load_2d_cg2(sa, &tmA, &full_bar[stage], k0, m0);
+          tma_load_2d_cg2_hint(sa, &tmA, &full_bar[stage], k0, m0, pol_a);
           if (kBKmajor) {
             tma_load_2d_cg2(sb, &tmB, &full_bar[stage], k0, n0);
           } else {

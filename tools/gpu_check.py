@@ -227,7 +227,7 @@ def main():
         import ctypes
         lib = capi.load()
         lib.b200_attention_set_profile_buffer.argtypes = [ctypes.c_void_p]
-        capi.set_attention_variant(2)
+        capi.set_attention_variant(args.g if args.g else 2)
         buf = torch.zeros(8, dtype=torch.int64, device="cuda")
         B, S, H, D = 8, 4096, 32, 128
         q, k, v = (torch.randn(B, S, H, D, device="cuda").to(torch.bfloat16) for _ in range(3))
@@ -240,7 +240,9 @@ def main():
         lib.b200_attention_set_profile_buffer(None)
         t = buf.cpu().tolist()
         nt = max(t[6], 1)
-        names = ["wait s_full", "tmem ld S", "mask+max+decide", "wait pv_done", "exp + P store", "fence + arrive"]
+        names = (["wait s_full", "tmem ld S", "mask+max+decide", "rescale O (if any)", "exp (P in regs)", "tmem st P + arrive"]
+                 if args.g == 4 else
+                 ["wait s_full", "tmem ld S", "mask+max+decide", "wait pv_done", "exp + P store", "fence + arrive"])
         print(f"  softmax warp 4 of block (0,0,0): {nt} KV tiles, cycles per tile:")
         for n, c in zip(names, t[:6]):
             print(f"    {n:18s} {c / nt:8.0f}")
