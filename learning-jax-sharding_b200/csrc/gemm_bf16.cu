@@ -144,10 +144,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // ===================== TMA producer (whole warp in the loop, one elected lane issues) =====================
     int stage = 0;
     uint32_t phase = 0;
-    // A row-panels of the current raster group are re-read by every column block of the group: ask L2 to keep
-    // them (evict_last).  B keeps the default policy: its tiles are shared by the group_m CTAs that run next to
-    // each other, and evict_first made them miss (measured: DRAM reads 1.2 -> 3.4 GB, profiles/r01_l2_hint_experiment.md).
-    const uint64_t pol_a = l2_policy_evict_last();
+    // (L2 eviction hints were tried and removed: evict_first on B made the B tiles shared by neighbouring CTAs
+    //  miss, evict_last on A did not keep a 67 MB panel group resident -- profiles/r01_l2_hint_experiment.md.)
     for (int tile = worker; tile < num_tiles; tile += num_workers) {
       int m_blk, n_blk;
       tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, m_blk, n_blk);
@@ -165,7 +163,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (elect_one()) {
         if (G == 1) {
           mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
-          tma_load_2d_hint(sa, &tmA, &full_bar[stage], k0, m0, pol_a);
+          tma_load_2d(sa, &tmA, &full_bar[stage], k0, m0);
           if (kBKmajor) {
             tma_load_2d(sb, &tmB, &full_bar[stage], k0, n0);
           } else {
@@ -176,7 +174,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         } else {
           // both CTAs' bytes complete on the leader's barrier
           if (leader) mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes * 2);
-          tma_load_2d_cg2_hint(sa, &tmA, &full_bar[stage], k0, m0, pol_a);
+          tma_load_2d_cg2(sa, &tmA, &full_bar[stage], k0, m0);
           if (kBKmajor) {
             tma_load_2d_cg2(sb, &tmB, &full_bar[stage], k0, n0);
           } else {
@@ -399,13 +397,11 @@ static int launch_gemm(const void* A, int64_t lda, const void* B, int64_t ldb, c
   if (g_group_m > 0) {
     p.group_m = g_group_m;
   } else {
-    // Raster group = the A row-panels (group_m x 128*G rows x K) that stay L2-resident (~64 MB of the 126 MB)
-    // while the B panels stream past once per group.  ncu: at group 8 the K=4096 FFN GEMM re-read B eight
-    // times (1.23 GB read vs 0.27 GB algorithmic, profiles/r01_ncu_gemm_full_summary_v2.txt); speed is flat
-    // within noise (r01_gemm_sweep2.log), the DRAM bytes are what this saves.
-    const int64_t panel_bytes = static_cast<int64_t>(kBM) * G * p.K * 2;
-    const int64_t gm = (64ll << 20) / (panel_bytes > 0 ? panel_bytes : 1);
-    p.group_m = static_cast<int>(gm < 4 ? 4 : (gm > 32 ? 32 : gm));
+    // Raster group (row-blocks that sweep all column-blocks together).  Measured with ncu on the two FFN GEMMs
+    // (profiles/r01_gemm_dram_traffic_vs_raster.log): at K = 4096 group 16 reads 0.95 GB from DRAM (8: 1.29,
+    // 32: 2.36, 4: 2.40; 0.27 GB algorithmic) and is also the fastest; at K = 16384 the panels of one wave
+    // alone are ~145 MB > L2 and every group size reads 3.2-4 GB, so the choice is flat.
+    p.group_m = p.K <= 8192 ? 16 : 8;
   }
   CUtensorMap tmA, tmB;
   {

@@ -247,6 +247,18 @@ def main():
         for n, c in zip(names, t[:6]):
             print(f"    {n:18s} {c / nt:8.0f}")
         print(f"    {'total':18s} {sum(t[:6]) / nt:8.0f}", flush=True)
+    elif args.what == "gemm_traffic":
+        # run under: ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum -k regex:gemm_bf16
+        for (M, N, K, gms) in [(16384, 16384, 4096, (4, 8, 16, 32)), (16384, 4096, 16384, (2, 4, 8, 16))]:
+            a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
+            b = torch.randn(K, N, device="cuda").to(torch.bfloat16)
+            out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+            for gm in gms:
+                capi.set_gemm_group_m(gm)
+                capi.gemm_bf16(a, b, out=out)
+                torch.cuda.synchronize()
+                print(f"  launched M={M} N={N} K={K} group_m={gm}", flush=True)
+        capi.set_gemm_group_m(0)
     elif args.what == "attn_prof":
         q, k, v = (torch.randn(2, 4096, 16, 128, device="cuda").to(torch.bfloat16) for _ in range(3))
         for _ in range(3):
