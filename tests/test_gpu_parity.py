@@ -342,3 +342,22 @@ def test_sharded_mha_layer_one_gpu(ljs, causal):
     y = layer.forward(bf(x)).cpu().reshape(B, S, M)
     want = rm.mha_forward(x, params, H, D, causal)
     torch.testing.assert_close(y.float(), want.float(), **BF16_TOL)
+
+
+def test_host_buffer_ffn_step_matches_oracle(ljs):
+    """The end-to-end call bench.py times as `e2e` (x in pinned host memory -> chunked H2D | GEMMs | D2H -> y in
+    pinned host memory) returns what the oracle computes from the same seeded tensors."""
+    from learning_jax_sharding_b200 import layers
+    cfg = dict(batch=2, seq=1024, d_model=512, d_ff=2048, parallelism="tp")
+    bench = layers.FFNBench(cfg, "gelu_tanh", rank=0, world=1, dev=torch.device("cuda", 0))
+    y_host = bench.step_e2e()
+    torch.cuda.synchronize()
+    x = rm.synthetic((2048, 512), 0)
+    w1, b1 = rm.synthetic((512, 2048), 1, "weight"), rm.synthetic((2048,), 2, "bias")
+    w2, b2 = rm.synthetic((2048, 512), 3, "weight"), rm.synthetic((512,), 4, "bias")
+    want = rm.ffn_forward(x, w1, b1, w2, b2, "gelu_tanh")
+    torch.testing.assert_close(y_host.float(), want.float(), **BF16_TOL)
+    # and the resident-input step gives the same tensor
+    y_dev = bench.step_resident()
+    torch.cuda.synchronize()
+    torch.testing.assert_close(y_dev.cpu().float(), y_host.float(), rtol=0, atol=0)
