@@ -297,10 +297,12 @@ class FsdpFFN:
 
 class PeerGatherFFN:
     """FSDP layout without NCCL on the data path: every rank keeps its dim0-shard of W1 and W2 in
-    CUDA-IPC-shared memory; a forward pass PULLS the other ranks' shards straight out of their HBM with
-    copy-engine peer copies (no SM time, no cross-rank synchronisation -- weights are read-only), one
-    column chunk at a time on side streams, while the GEMM of the previous chunk runs.  Pull order is
-    staggered by rank so every source serves one reader at a time."""
+    CUDA-IPC-shared memory, stored COLUMN-CHUNK-MAJOR ([chunk][rows][cols/chunks]); a forward pass PULLS the
+    other ranks' shards straight out of their HBM, one column chunk at a time, while the GEMM of the previous
+    chunk runs.  Because both the source chunk and its place in the chunk-major gathered matrix are contiguous,
+    every pull is a plain 1-D peer copy on the copy engines (mode "ce": no SM time) -- or one SM kernel per chunk
+    (mode "kernel", b200_peer_gather).  No cross-rank synchronisation is needed: weights are read-only.  Pull
+    order is staggered by rank so every source serves one reader at a time."""
 
     def __init__(self, w1_shard, b1, w2_shard, b2, act: str, T_local: int, group, chunks: int = 4, copy_streams: int = 4,
                  mode: str = "ce", ctas: int = 48):
@@ -312,48 +314,50 @@ class PeerGatherFFN:
         self.k1, self.F = w1_shard.shape            # rows of W1 held here, d_ff
         self.k2, self.d_model = w2_shard.shape      # rows of W2 held here, d_model
         self.T = T_local
-        self.chunks = chunks
+        self.chunks = C = chunks
+        self.mode, self.ctas = mode, ctas
         dev = w1_shard.device
         n1, n2 = w1_shard.numel() * 2, w2_shard.numel() * 2
+        self.n1 = n1
         self.base, handle = capi.peer_alloc(n1 + n2)
-        # place the shards in the shared allocation
-        capi.peer_copy2d(self.base, n1, w1_shard.data_ptr(), n1, n1, 1, torch.cuda.current_stream(dev))
-        capi.peer_copy2d(self.base + n1, n2, w2_shard.data_ptr(), n2, n2, 1, torch.cuda.current_stream(dev))
+        # chunk-major copies of the local shards inside the shared allocation
+        w1c = w1_shard.reshape(self.k1, C, self.F // C).permute(1, 0, 2).contiguous()
+        w2c = w2_shard.reshape(self.k2, C, self.d_model // C).permute(1, 0, 2).contiguous()
+        cur = torch.cuda.current_stream(dev)
+        capi.peer_copy2d(self.base, n1, w1c.data_ptr(), n1, n1, 1, cur)
+        capi.peer_copy2d(self.base + n1, n2, w2c.data_ptr(), n2, n2, 1, cur)
         torch.cuda.synchronize(dev)
+        del w1c, w2c
         mine = torch.tensor(list(handle), dtype=torch.uint8, device=dev)
         handles = [torch.empty_like(mine) for _ in range(W)]
         dist.all_gather(handles, mine, group=group)
         self.peer_base = [self.base if p == self.rank else capi.peer_open(bytes(handles[p].cpu().tolist()))
                           for p in range(W)]
-        self.n1 = n1
-        self.mode, self.ctas = mode, ctas          # "kernel": b200_peer_gather (SM pull); "ce": copy-engine 2-D copies
         self.src_bases = torch.tensor(self.peer_base, dtype=torch.int64, device=dev)
-        self.w1g = torch.empty((self.k1 * W, self.F), dtype=torch.bfloat16, device=dev)
-        self.w2g = torch.empty((self.k2 * W, self.d_model), dtype=torch.bfloat16, device=dev)
+        # gathered weights, chunk-major: [chunk][W * rows][cols / chunks]
+        self.w1g = torch.empty((C, self.k1 * W, self.F // C), dtype=torch.bfloat16, device=dev)
+        self.w2g = torch.empty((C, self.k2 * W, self.d_model // C), dtype=torch.bfloat16, device=dev)
         self.h = torch.empty((T_local, self.F), dtype=torch.bfloat16, device=dev)
         self.y = torch.empty((T_local, self.d_model), dtype=torch.bfloat16, device=dev)
         self.streams = [torch.cuda.Stream(device=dev) for _ in range(copy_streams)]
         self.ready = [[torch.cuda.Event() for _ in range(copy_streams)] for _ in range(2 * chunks)]
         dist.barrier(group=group)
 
-    def _pull(self, which: int, j: int, main):
+    def _pull(self, which: int, j: int):
         """Enqueue the pulls of column chunk j of weight `which` (0 = W1, 1 = W2) from every rank."""
         W, C = self.world, self.chunks
         rows, cols = (self.k1, self.F) if which == 0 else (self.k2, self.d_model)
         dst = self.w1g if which == 0 else self.w2g
-        cw = cols // C
+        blk = rows * (cols // C) * 2                          # bytes of one rank's chunk (contiguous on both sides)
+        src_off = (0 if which == 0 else self.n1) + j * blk
+        dst0 = dst.data_ptr() + j * W * blk
         if self.mode == "kernel":
-            st = self.streams[0]
-            capi.peer_gather(self.src_bases, W, self.rank, (0 if which == 0 else self.n1) + j * cw * 2, cols * 2,
-                             dst.data_ptr() + j * cw * 2, cols * 2, rows, cw * 2, self.ctas, st)
-            for k, s_ in enumerate(self.streams):
-                self.ready[which * C + j][k].record(s_)
-            return
-        for i in range(W):
-            p = (self.rank + 1 + i) % W                       # own shard last
-            st = self.streams[i % len(self.streams)]
-            src = self.peer_base[p] + (0 if which == 0 else self.n1) + j * cw * 2
-            capi.peer_copy2d(dst.data_ptr() + (p * rows * cols + j * cw) * 2, cols * 2, src, cols * 2, cw * 2, rows, st)
+            capi.peer_gather(self.src_bases, W, self.rank, src_off, blk, dst0, blk, 1, blk, self.ctas, self.streams[0])
+        else:
+            for i in range(W):
+                p = (self.rank + 1 + i) % W                   # own shard last
+                st = self.streams[i % len(self.streams)]
+                capi.peer_copy2d(dst0 + p * blk, blk, self.peer_base[p] + src_off, blk, blk, 1, st)
         for k, st in enumerate(self.streams):
             self.ready[which * C + j][k].record(st)
 
@@ -363,9 +367,9 @@ class PeerGatherFFN:
         for st in self.streams:
             st.wait_stream(main)                              # the previous step's GEMMs have read w1g / w2g
         for j in range(C):
-            self._pull(0, j, main)
+            self._pull(0, j)
         for j in range(C):
-            self._pull(1, j, main)
+            self._pull(1, j)
         fc, dc = self.F // C, self.d_model // C
         for j in range(C):
             for ev in self.ready[j]:
@@ -373,7 +377,7 @@ class PeerGatherFFN:
             if record is not None:
                 record("start")
             b = self.b1[j * fc:(j + 1) * fc] if self.b1 is not None else None
-            capi.gemm_bf16(x, self.w1g[:, j * fc:(j + 1) * fc], bias=b, epilogue=self.act, out=self.h[:, j * fc:(j + 1) * fc])
+            capi.gemm_bf16(x, self.w1g[j], bias=b, epilogue=self.act, out=self.h[:, j * fc:(j + 1) * fc])
             if record is not None:
                 record("gemm1")
         for j in range(C):
@@ -382,8 +386,8 @@ class PeerGatherFFN:
             if record is not None:
                 record("start")
             b = self.b2[j * dc:(j + 1) * dc] if self.b2 is not None else None
-            capi.gemm_bf16(self.h, self.w2g[:, j * dc:(j + 1) * dc], bias=b,
-                           epilogue=capi.EPI_BIAS if b is not None else capi.EPI_NONE, out=self.y[:, j * dc:(j + 1) * dc])
+            capi.gemm_bf16(self.h, self.w2g[j], bias=b, epilogue=capi.EPI_BIAS if b is not None else capi.EPI_NONE,
+                           out=self.y[:, j * dc:(j + 1) * dc])
             if record is not None:
                 record("gemm2")
         return self.y
