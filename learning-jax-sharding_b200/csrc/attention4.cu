@@ -24,6 +24,10 @@
 
 namespace b200 {
 
+#ifndef B200_ATTN_PROFILE
+#define B200_ATTN_PROFILE 0   // 1: per-phase clock64 totals of one warp into Params::prof (tools/gpu_check.py attn_phases)
+#endif
+
 constexpr int kA4BM = 128;      // rows per query tile
 constexpr int kA4BN = 128;      // keys per KV tile
 constexpr int kA4Threads = 384;
@@ -243,10 +247,14 @@ attention_fwd4_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     const uint32_t o_tmem = lane_base + Cfg::kOCol + q * 128;
     float m_used = -INFINITY;
     float l_sum = 0.f;
-    const bool prof = p.prof != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && warp == 4 && lane == 0;
+    const bool prof = B200_ATTN_PROFILE && p.prof != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && warp == 4 && lane == 0;
     long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    long long tp = clock64();
+    long long tp = prof ? clock64() : 0;
+#if B200_ATTN_PROFILE
 #define PROF_MARK4(k) do { if (prof) { long long _t = clock64(); tacc[k] += _t - tp; tp = _t; } } while (0)
+#else
+#define PROF_MARK4(k) do { } while (0)
+#endif
     for (int j = 0; j < nt; ++j) {
       const int t0 = j * kA4BN;
       int limit = p.Sk - t0;

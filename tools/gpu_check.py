@@ -224,11 +224,12 @@ def main():
             lib.b200_gemm_set_max_stages(0)
             capi.set_gemm_group_m(0)
     elif args.what == "attn_phases":
+        # needs a build with B200_EXTRA_NVCC_FLAGS=-DB200_ATTN_PROFILE=1 (the hooks are compiled out by default)
         import ctypes
         lib = capi.load()
         lib.b200_attention_set_profile_buffer.argtypes = [ctypes.c_void_p]
         capi.set_attention_variant(args.g if args.g else 2)
-        buf = torch.zeros(8, dtype=torch.int64, device="cuda")
+        buf = torch.zeros(16, dtype=torch.int64, device="cuda")
         B, S, H, D = 8, 4096, 32, 128
         q, k, v = (torch.randn(B, S, H, D, device="cuda").to(torch.bfloat16) for _ in range(3))
         o = torch.empty_like(q)
@@ -239,6 +240,18 @@ def main():
         torch.cuda.synchronize()
         lib.b200_attention_set_profile_buffer(None)
         t = buf.cpu().tolist()
+        if args.g == 5:
+            nt = max(t[7], 1)
+            names5 = ["wait s_full", "tmem ld S + s_free", "mask + half max", "xchg barrier", "decide / rescale / P-buffer wait",
+                      "exp", "tmem st P + arrive"]
+            print(f"  v5 softmax warp 4 of block (0,0,0): {nt} KV tiles, cycles per tile:")
+            for n, c in zip(names5, t[:7]):
+                print(f"    {n:34s} {c / nt:8.0f}")
+            print(f"    {'total':34s} {sum(t[:7]) / nt:8.0f}")
+            print(f"  MMA warp: {t[8] / nt:.0f} cycles per tile in the loop, {t[9] / nt:.0f} issuing, {t[10] / nt:.1f} polls per tile",
+                  flush=True)
+            print("RESULT PASS")
+            return
         nt = max(t[6], 1)
         names = (["wait s_full", "tmem ld S", "mask+max+decide", "rescale O (if any)", "exp (P in regs)", "tmem st P + arrive"]
                  if args.g == 4 else
