@@ -345,9 +345,12 @@ int attention_fwd4_dispatch(const void* Q, const void* K, const void* V, void* O
                             const int64_t* strides, float scale, int causal, cudaStream_t stream);
 int attention_fwd5_dispatch(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
                             const int64_t* strides, float scale, int causal, cudaStream_t stream);
+int attention_fwd6_dispatch(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
+                            const int64_t* strides, float scale, int causal, cudaStream_t stream);
 // 0 = auto; 1 = one query tile per CTA; 2 = two query tiles, 128-key tiles, P through smem; 3 = two query tiles,
 // 64-key tiles, double-buffered S and P; 4 = two query tiles, 128-key tiles, P kept in TMEM (A operand of P.V);
-// 5 = one query tile, S and P double-buffered in TMEM, softmax rows split over two warp groups
+// 5 = one query tile, S and P double-buffered in TMEM, softmax rows split over two warp groups;
+// 6 = v5 with Q in TMEM as well (both MMAs take A from TMEM)
 static int g_attn_variant = 0;
 
 }  // namespace b200
@@ -362,7 +365,7 @@ extern "C" int b200_attention_set_profile_buffer(void* dev_buf) {
 }
 
 extern "C" int b200_attention_set_variant(int variant) {
-  if (variant < 0 || variant > 5) return fail(B200_ERR_INVALID_ARGUMENT, "attention variant must be 0..5");
+  if (variant < 0 || variant > 6) return fail(B200_ERR_INVALID_ARGUMENT, "attention variant must be 0..6");
   g_attn_variant = variant;
   return B200_OK;
 }
@@ -385,6 +388,7 @@ extern "C" int b200_attention_fwd(const void* Q, const void* K, const void* V, v
                 reinterpret_cast<uintptr_t>(O)) % 16 == 0,
                "b200_attention_fwd: operands must be 16-byte aligned");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (g_attn_variant == 6) return attention_fwd6_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
   if (g_attn_variant == 5) return attention_fwd5_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
   if (g_attn_variant == 4) return attention_fwd4_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
   if (g_attn_variant == 3) return attention_fwd3_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);

@@ -197,7 +197,7 @@ def test_attention_against_golden(ljs, d, causal):
                                    (2, 100, 1000, 2, 64), (1, 1024, 1024, 4, 128), (1, 384, 640, 2, 128),
                                    (1, 1300, 1300, 1, 64)])
 @pytest.mark.parametrize("causal", [False, True])
-@pytest.mark.parametrize("variant", [1, 2, 3, 4, 5])
+@pytest.mark.parametrize("variant", [1, 2, 3, 4, 5, 6])
 def test_attention_ragged_shapes(ljs, shape, causal, variant):
     ljs.capi.set_attention_variant(variant)      # 1 = one query tile per CTA, 2 / 3 = two tiles (128- / 64-key KV tiles)
     B, Sq, Sk, H, D = shape
