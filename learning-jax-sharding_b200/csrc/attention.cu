@@ -347,10 +347,19 @@ int attention_fwd5_dispatch(const void* Q, const void* K, const void* V, void* O
                             const int64_t* strides, float scale, int causal, cudaStream_t stream);
 int attention_fwd6_dispatch(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
                             const int64_t* strides, float scale, int causal, cudaStream_t stream);
+int attention_fwd7_dispatch(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
+                            const int64_t* strides, float scale, int causal, cudaStream_t stream);
+int attention_fwd8_dispatch(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
+                            const int64_t* strides, float scale, int causal, cudaStream_t stream);
+int attention_fwd9_dispatch(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
+                            const int64_t* strides, float scale, int causal, cudaStream_t stream);
 // 0 = auto; 1 = one query tile per CTA; 2 = two query tiles, 128-key tiles, P through smem; 3 = two query tiles,
 // 64-key tiles, double-buffered S and P; 4 = two query tiles, 128-key tiles, P kept in TMEM (A operand of P.V);
 // 5 = one query tile, S and P double-buffered in TMEM, softmax rows split over two warp groups;
-// 6 = v5 with Q in TMEM as well (both MMAs take A from TMEM)
+// 6 = v5 with Q in TMEM as well (both MMAs take A from TMEM);
+// 7 = one query tile, the two softmax warp groups on alternate KV tiles (whole rows per thread);
+// 8 = v7 as a persistent kernel (one CTA per SM walks a static work list, items overlap);
+// 9 = v8 on CTA pairs (cta_group::2 MMAs, K / V tiles loaded once per 256 query rows), head dim 128 only
 static int g_attn_variant = 0;
 
 }  // namespace b200
@@ -365,7 +374,7 @@ extern "C" int b200_attention_set_profile_buffer(void* dev_buf) {
 }
 
 extern "C" int b200_attention_set_variant(int variant) {
-  if (variant < 0 || variant > 6) return fail(B200_ERR_INVALID_ARGUMENT, "attention variant must be 0..6");
+  if (variant < 0 || variant > 9) return fail(B200_ERR_INVALID_ARGUMENT, "attention variant must be 0..9");
   g_attn_variant = variant;
   return B200_OK;
 }
@@ -388,15 +397,20 @@ extern "C" int b200_attention_fwd(const void* Q, const void* K, const void* V, v
                 reinterpret_cast<uintptr_t>(O)) % 16 == 0,
                "b200_attention_fwd: operands must be 16-byte aligned");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (g_attn_variant == 9) return attention_fwd9_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
+  if (g_attn_variant == 8) return attention_fwd8_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
+  if (g_attn_variant == 7) return attention_fwd7_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
   if (g_attn_variant == 6) return attention_fwd6_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
   if (g_attn_variant == 5) return attention_fwd5_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
   if (g_attn_variant == 4) return attention_fwd4_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
   if (g_attn_variant == 3) return attention_fwd3_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
-  // auto: measured best per head dim (profiles/r01_attention_v5.md): D = 128 -> v5 (1073 vs 1019 TFLOP/s for v2),
-  // D = 64 -> v2 (617 vs 565)
+  // auto: measured best per head dim (profiles/r01_attention_v7.md): D = 128 -> v9 (CTA pairs, 1223 TFLOP/s vs 1176 for
+  // v8 and 1084 for v5), D = 64 -> v8 (662 vs 617 for v2); a single query tile stays on v1
   if (g_attn_variant == 0 && Sq > kAttnBM && D == 128)
-    return attention_fwd5_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
-  if (g_attn_variant == 2 || (g_attn_variant == 0 && Sq > kAttnBM))
+    return attention_fwd9_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
+  if (g_attn_variant == 0 && Sq > kAttnBM && D == 64)
+    return attention_fwd8_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
+  if (g_attn_variant == 2)
     return attention_fwd2_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
   AttnParams p = {};
   p.O = reinterpret_cast<__nv_bfloat16*>(O);

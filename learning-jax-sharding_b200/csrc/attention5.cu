@@ -3,7 +3,8 @@
 // attention.cu (reference order case6_attention.py:121-135: f32 scores, f32 softmax, bf16 P, f32-accumulated
 // P.V, bf16 out).
 //
-// Why this shape (measurements in profiles/r01_smem_operand_bandwidth_model.md, r01_attention_v*_phase_cycles.log):
+// Why this shape (as understood when it was written; profiles/r01_mma_rate_microbench.md later showed the MMA costs to be
+// 107 cycles with A in smem / 74 with A in TMEM, and profiles/r01_attention_v7.md what really bounded this kernel):
 //   * a 128x128x16 MMA fed from shared memory runs at half rate (operand fetch ~64 B/clk), so P must not
 //     take the smem route: P stays in TMEM and feeds P.V as the TMEM A operand (tcgen05.mma TS form);
 //   * with two query tiles per CTA the 512 TMEM columns are used up by S0,S1,O0,O1, P has to alias S and

@@ -1,0 +1,473 @@
+// Attention forward, ONE 128-row query tile per CTA, S and P double-buffered in tensor memory, and the two
+// softmax warp groups working on ALTERNATE KV tiles (group 0: even tiles, group 1: odd tiles), each thread owning
+// a whole 128-key score row.  Same math and layout as attention.cu (reference order case6_attention.py:121-135:
+// f32 scores, f32 softmax, bf16 P, f32-accumulated P.V, bf16 out).
+//
+// Why (profiles/r01_mma_rate_microbench.md, r01_attention_v5.md): alone on an SM a 128x128x16 tcgen05.mma costs
+// 107 cycles with A in shared memory and 74 with A in TMEM, so Q.K^T + P.V need ~1400 cycles per 128 keys; the
+// softmax of attention5.cu takes ~2150 because both warp groups run the SAME tile in lockstep (they exchange half
+// row maxima through a 256-thread barrier) and the MUFU, saturated during the exp pass, idles during the load /
+// max / wait phases.  Here the groups are out of phase by construction, so one group's exp pass overlaps the
+// other's load + max, and no row is split across threads (no exchange barrier).  What still couples the groups is
+// the running reference max: the softmax is ONE sequence over tiles, so tile j takes over the reference max that
+// tile j-1 settled on (a 4-byte shared-memory hand-off per row, guarded by one mbarrier per lane quadrant and tile
+// parity), rescales O itself in the rare case it raises the max by more than 2^8, and each group keeps its own
+// partial row sum relative to the max it last used; the two sums meet once in the epilogue.
+//
+//   warp 0        TMA producer: Q once, then K_0,K_1,V_0,K_2,V_1,... through one smem ring (6 tiles at D = 128)
+//   warp 1        MMA issuer (whole warp polls, one elected lane issues)
+//   warp 2        TMEM allocator
+//   warps 4..7    softmax group 0: KV tiles 0,2,4,... through S[0] / P[0]
+//   warps 8..11   softmax group 1: KV tiles 1,3,5,... through S[1] / P[1]
+// TMEM: S[2] (2 x 128 columns) + P[2] (2 x 64) + O (128) = 512 columns, nothing aliases.
+#include <cuda.h>
+#include <math.h>
+
+#include "host_common.h"
+#include "sm100_ptx.cuh"
+
+namespace b200 {
+
+#ifndef B200_ATTN_PROFILE
+#define B200_ATTN_PROFILE 0   // 1: per-phase clock64 totals of one warp into Params::prof (tools/gpu_check.py attn_phases)
+#endif
+
+constexpr int kA7BM = 128;      // query rows per CTA
+constexpr int kA7BN = 128;      // keys per KV tile
+constexpr int kA7Threads = 384;
+constexpr float kA7Rescale = 8.0f;
+template <int D>
+struct Attn7Cfg {
+  static constexpr int kQBytes = kA7BM * D * 2;
+  static constexpr int kKVBytes = kA7BN * D * 2;
+  static constexpr int kXchgBytes = 2 * 2 * kA7BM * 4;   // reference max [tile parity][row] + row sums [group][row]
+  static constexpr int kBudget = 227 * 1024 - 1024 - 512 - kXchgBytes - kQBytes;
+  static constexpr int kStages = kBudget / kKVBytes > 8 ? 8 : kBudget / kKVBytes;
+  static constexpr int kSmemBytes = kQBytes + kStages * kKVBytes + kXchgBytes + 1024 + 512;
+  static constexpr int kTmemCols = 512;
+  static constexpr int kSCol = 0;       // S[b] at 128 b
+  static constexpr int kPCol = 256;     // P[b] at 256 + 64 b (bf16 pairs: 64 columns = 128 keys)
+  static constexpr int kOCol = 384;     // O: D columns
+};
+
+struct Attn7Params {
+  __nv_bfloat16* O;
+  int Sq, Sk;
+  int64_t o_stride_b, o_stride_s, o_stride_h;
+  float scale_log2;
+  int causal;
+  int num_q_tiles;
+  long long* prof;   // optional bring-up aid: per-phase cycle totals of block (0,0,0): softmax warp 4 -> [0..7], MMA warp -> [8..15]
+};
+
+__device__ __forceinline__ float max3k(float a, float b, float c) {
+  float r;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+  return r;
+}
+__device__ __forceinline__ void softmax_pair_barrier7() {     // the 256 softmax threads (warps 4..11)
+  asm volatile("bar.sync 1, 256;" ::: "memory");
+}
+
+template <int D>
+__global__ void __launch_bounds__(kA7Threads, 1)
+attention_fwd7_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                      const __grid_constant__ CUtensorMap tmV, const Attn7Params p) {
+  using Cfg = Attn7Cfg<D>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sKV = sQ + Cfg::kQBytes;
+  float* mref = reinterpret_cast<float*>(sKV + Cfg::kStages * Cfg::kKVBytes);   // [tile parity][row]
+  float* lsum_x = mref + 2 * kA7BM;                                             // [group][row]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(mref) + Cfg::kXchgBytes);
+  uint64_t* q_full = bars;                              // 1
+  uint64_t* kv_full = bars + 1;                         // kStages
+  uint64_t* kv_empty = kv_full + Cfg::kStages;          // kStages
+  uint64_t* s_full = kv_empty + Cfg::kStages;           // 2 (one MMA commit)
+  uint64_t* s_free = s_full + 2;                        // 2 (4 warp arrivals: one group each)
+  uint64_t* p_full = s_free + 2;                        // 2 (4 warp arrivals)
+  uint64_t* pv_done = p_full + 2;                       // 2 (one MMA commit)
+  uint64_t* m_ready = pv_done + 2;                      // [tile parity][quadrant]: reference max of a tile published
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(m_ready + 8);
+
+  const int warp = uniform_warp_idx();
+  const int lane = threadIdx.x & 31;
+  const int q_tile = p.causal ? (p.num_q_tiles - 1 - blockIdx.x) : blockIdx.x;   // heaviest first
+  const int head = blockIdx.y;
+  const int batch = blockIdx.z;
+  const int f0 = q_tile * kA7BM;
+  const int off = p.Sk - p.Sq;
+  int kv_len = p.Sk;
+  if (p.causal) kv_len = min(p.Sk, f0 + kA7BM + off);
+  const int nt = (kv_len + kA7BN - 1) / kA7BN;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmK);
+    tma_prefetch_desc(&tmV);
+  }
+  if (warp == 1 && lane == 0) {
+    mbar_init(q_full, 1);
+    for (int s = 0; s < Cfg::kStages; ++s) {
+      mbar_init(&kv_full[s], 1);
+      mbar_init(&kv_empty[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&s_full[b], 1);
+      mbar_init(&s_free[b], 4);
+      mbar_init(&p_full[b], 4);
+      mbar_init(&pv_done[b], 1);
+    }
+    for (int i = 0; i < 8; ++i) mbar_init(&m_ready[i], 1);
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc<Cfg::kTmemCols>(tmem_ptr_smem);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  // register re-split: the control warp group needs few, each softmax thread keeps a 128-wide score row
+  if (warp < 4) {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (elect_one()) {
+      mbar_arrive_expect_tx(q_full, Cfg::kQBytes);
+#pragma unroll
+      for (int c = 0; c < D / 64; ++c) tma_load_4d(sQ + c * (kA7BM * 128), &tmQ, q_full, c * 64, head, f0, batch);
+      int item = 0;
+      auto load = [&](const CUtensorMap* tm, int j) {
+        const int st = item % Cfg::kStages;
+        const uint32_t ph = (item / Cfg::kStages) & 1;
+        ++item;
+        mbar_wait(&kv_empty[st], ph ^ 1);
+        mbar_arrive_expect_tx(&kv_full[st], Cfg::kKVBytes);
+#pragma unroll
+        for (int c = 0; c < D / 64; ++c)
+          tma_load_4d(sKV + st * Cfg::kKVBytes + c * (kA7BN * 128), tm, &kv_full[st], c * 64, head, j * kA7BN, batch);
+      };
+      // K one tile ahead of V: K_0, K_1, V_0, K_2, V_1, ...
+      if (nt > 0) load(&tmK, 0);
+      for (int j = 0; j < nt; ++j) {
+        if (j + 1 < nt) load(&tmK, j + 1);
+        load(&tmV, j);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    constexpr uint32_t idesc_qk = make_idesc_bf16(kA7BM, kA7BN, false, false);
+    constexpr uint32_t idesc_pv = make_idesc_bf16(kA7BM, D, false, true);
+    const uint64_t q_desc0 = make_smem_desc_sw128(smem_u32(sQ), 16, 1024);
+    const uint64_t k_desc0 = make_smem_desc_sw128(smem_u32(sKV), 16, 1024);
+    const uint64_t v_desc0 = make_smem_desc_sw128(smem_u32(sKV), kA7BN * 128, 1024);
+    int next_qk = 0, next_pv = 0;
+    mbar_wait(q_full, 0);
+    uint32_t idle = 0;
+    const bool mprof = B200_ATTN_PROFILE && p.prof != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
+    long long m_t0 = mprof ? clock64() : 0, m_issue = 0, m_polls = 0;
+    while (next_pv < nt) {
+      bool progressed = false;
+      // ---- O += P(j) . V_j : first, it is what the softmax two tiles later and the epilogue wait for
+      if (next_pv < next_qk) {
+        const int j = next_pv, b = j & 1;
+        const int i = (j + 1 < nt) ? 2 * j + 2 : 2 * j + 1, st = i % Cfg::kStages;   // ring position of V_j
+        const uint32_t ph = (i / Cfg::kStages) & 1;
+        if (mbar_test_wait(&p_full[b], (j >> 1) & 1) && mbar_test_wait(&kv_full[st], ph)) {
+          const long long ti = mprof ? clock64() : 0;
+          tc_fence_after();
+          if (elect_one()) {
+            const uint64_t vd = desc_advance(v_desc0, st * Cfg::kKVBytes);
+            const uint32_t p_tmem = tmem_base + Cfg::kPCol + b * 64;     // 16 keys = 8 columns per MMA
+            const uint32_t o_tmem = tmem_base + Cfg::kOCol;
+            if (j == 0) mma_bf16_ts_c<false>(o_tmem, p_tmem, vd, idesc_pv);
+            else mma_bf16_ts_c<true>(o_tmem, p_tmem, vd, idesc_pv);
+#pragma unroll
+            for (int kk = 1; kk < kA7BN / 16; ++kk)
+              mma_bf16_ts_c<true>(o_tmem, p_tmem + kk * 8, desc_advance(vd, kk * (16 * 128)), idesc_pv);
+            mma_commit(&pv_done[b]);
+            mma_commit(&kv_empty[st]);
+          }
+          __syncwarp();
+          if (mprof) m_issue += clock64() - ti;
+          ++next_pv;
+          progressed = true;
+        }
+      }
+      // ---- S[b] = Q . K_j^T, up to two tiles ahead of the softmax
+      if (next_qk < nt) {
+        const int j = next_qk, b = j & 1;
+        const int i = j == 0 ? 0 : 2 * j - 1, st = i % Cfg::kStages;                 // ring position of K_j
+        const uint32_t ph = (i / Cfg::kStages) & 1;
+        const bool s_ok = (j < 2) || mbar_test_wait(&s_free[b], ((j - 2) >> 1) & 1);
+        if (s_ok && mbar_test_wait(&kv_full[st], ph)) {
+          const long long ti = mprof ? clock64() : 0;
+          tc_fence_after();
+          if (elect_one()) {
+            const uint64_t kd = desc_advance(k_desc0, st * Cfg::kKVBytes);
+            const uint32_t s_tmem = tmem_base + Cfg::kSCol + b * 128;
+            mma_bf16_ss_c<false>(s_tmem, q_desc0, kd, idesc_qk);
+#pragma unroll
+            for (int kk = 1; kk < D / 16; ++kk) {
+              const uint32_t o = (kk >> 2) * (kA7BM * 128) + (kk & 3) * 32;
+              mma_bf16_ss_c<true>(s_tmem, desc_advance(q_desc0, o), desc_advance(kd, o), idesc_qk);
+            }
+            mma_commit(&s_full[b]);
+            mma_commit(&kv_empty[st]);
+          }
+          __syncwarp();
+          if (mprof) m_issue += clock64() - ti;
+          ++next_qk;
+          progressed = true;
+        }
+      }
+      if (mprof) ++m_polls;
+#if B200_WATCHDOG
+      if (progressed) {
+        idle = 0;
+      } else if (++idle > (1u << 26)) {
+        if (lane == 0)
+          printf("b200: attention7 MMA scheduler stuck block=(%d,%d,%d) qk=%d pv=%d nt=%d\n", (int)blockIdx.x,
+                 (int)blockIdx.y, (int)blockIdx.z, next_qk, next_pv, nt);
+        __trap();
+      }
+#endif
+    }
+    if (mprof && lane == 0) {
+      p.prof[8] = clock64() - m_t0;
+      p.prof[9] = m_issue;
+      p.prof[10] = m_polls;
+    }
+  }
+  } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");
+    // ===================== softmax / correction / epilogue =====================
+    const int grp = (warp - 4) >> 2;             // KV tiles j with (j & 1) == grp; O columns [grp*D/2, +D/2) in the epilogue
+    const int quad = warp & 3;                   // TMEM lane quadrant
+    const int row = quad * 32 + lane;
+    const int f = f0 + row;
+    const int b = grp;                           // S[b], P[b]: this group's buffers
+    const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
+    const uint32_t s_tmem = lane_base + Cfg::kSCol + b * 128;
+    const uint32_t p_tmem = lane_base + Cfg::kPCol + b * 64;
+    const uint32_t o_all = lane_base + Cfg::kOCol;
+    const uint64_t scale2 = pack_f32x2(p.scale_log2, p.scale_log2);
+    float m_local = -INFINITY;                   // the reference max l_part is relative to
+    float l_part = 0.f;                          // row sum over this group's tiles
+    const bool prof = B200_ATTN_PROFILE && p.prof != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && warp == 4 && lane == 0;
+    long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    long long tp = prof ? clock64() : 0;
+#if B200_ATTN_PROFILE
+#define PROF_MARK7(k) do { if (prof) { long long _t = clock64(); tacc[k] += _t - tp; tp = _t; } } while (0)
+#else
+#define PROF_MARK7(k) do { } while (0)
+#endif
+    for (int j = grp; j < nt; j += 2) {
+      const uint32_t use_ph = (j >> 1) & 1;
+      const int t0 = j * kA7BN;
+      int limit = p.Sk - t0;
+      if (p.causal) limit = min(limit, f + off + 1 - t0);
+      const bool need_mask = limit < kA7BN;
+      mbar_wait(&s_full[b], use_ph);
+      tc_fence_after();
+      PROF_MARK7(0);
+      uint32_t s[128];
+      {
+        uint32_t(&s0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[0]);
+        uint32_t(&s1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[32]);
+        uint32_t(&s2)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[64]);
+        uint32_t(&s3)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[96]);
+        tmem_ld_32x32(s_tmem, s0);
+        tmem_ld_32x32(s_tmem + 32, s1);
+        tmem_ld_32x32(s_tmem + 64, s2);
+        tmem_ld_32x32(s_tmem + 96, s3);
+        tmem_wait_ld();
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&s_free[b]);    // S[b] may be overwritten by Q.K^T of tile j+2
+      PROF_MARK7(1);
+      if (__any_sync(0xffffffffu, need_mask)) {
+        asm volatile("" ::: "memory");           // keep this a branch: only diagonal / tail tiles pay for masking
+#pragma unroll
+        for (int i = 0; i < 128; ++i)
+          if (i >= limit) s[i] = 0xff800000u;    // -inf
+      }
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+      for (int i = 0; i < 128; i += 8) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          mx4[c] = max3k(mx4[c], __uint_as_float(s[i + 2 * c]), __uint_as_float(s[i + 2 * c + 1]));
+      }
+      const float m_tile = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * p.scale_log2;
+      PROF_MARK7(2);
+      // The reference max is ONE sequence over all tiles: tile j starts from what tile j-1 (the other group's
+      // thread of the same row) settled on.  That hand-off is the only coupling between the two groups.
+      float m_prev = -INFINITY;
+      if (j > 0) {
+        mbar_wait(&m_ready[((j - 1) & 1) * 4 + quad], ((j - 1) >> 1) & 1);
+        m_prev = mref[((j - 1) & 1) * kA7BM + row];
+      }
+      PROF_MARK7(3);
+      float m_used = m_prev;
+      float factor = 1.0f;
+      bool rescale = false;
+      if (j == 0) {
+        m_used = m_tile;                         // key 0 is visible to every stored row, so this is finite
+      } else if (m_tile > m_prev + kA7Rescale) {
+        factor = exp2_approx(m_prev - m_tile);
+        m_used = m_tile;
+        rescale = true;
+      }
+      mref[(j & 1) * kA7BM + row] = m_used;
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&m_ready[(j & 1) * 4 + quad]);
+      if (m_used != m_local) {                   // bring this group's partial row sum to the current reference
+        l_part *= exp2_approx(m_local - m_used);
+        m_local = m_used;
+      }
+      if (__any_sync(0xffffffffu, rescale)) {
+        // O may only be touched once every P.V issued so far (tile j-1 is the last) has completed; P.V(j) cannot
+        // start before this warp has delivered P(j) below, and a rescale by tile j+1 waits for P.V(j) in turn.
+        mbar_wait(&pv_done[(j - 1) & 1], ((j - 1) >> 1) & 1);
+        tc_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < D / 32; ++c) {       // all D columns of this warp's 32 rows
+          uint32_t r[32];
+          tmem_ld_32x32(o_all + c * 32, r);
+          tmem_wait_ld();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * factor);
+          tmem_st_32x32(o_all + c * 32, r);
+        }
+        tmem_wait_st();
+      } else if (j >= 2) {
+        mbar_wait(&pv_done[b], ((j - 2) >> 1) & 1);   // P[b] has been read by P.V of tile j-2
+      }
+      PROF_MARK7(4);
+      // p = exp2(s * scale_log2 - m_used) -> bf16 pairs in place -> TMEM P[b]
+      const uint64_t negm2 = pack_f32x2(-m_used, -m_used);
+      uint64_t sum2[2] = {0ull, 0ull};
+#pragma unroll
+      for (int i = 0; i < 64; ++i) {
+        const uint64_t x2 = fma_f32x2(pack_f32x2(__uint_as_float(s[2 * i]), __uint_as_float(s[2 * i + 1])), scale2, negm2);
+        float x0, x1;
+        unpack_f32x2(x2, x0, x1);
+        const float p0 = exp2_approx(x0), p1 = exp2_approx(x1);
+        sum2[i & 1] = add_f32x2(sum2[i & 1], pack_f32x2(p0, p1));
+        s[i] = pack_bf16x2(p0, p1);              // keys (2i, 2i+1): low half = even key
+      }
+      {
+        float a0, a1, b0, b1;
+        unpack_f32x2(sum2[0], a0, a1);
+        unpack_f32x2(sum2[1], b0, b1);
+        l_part += (a0 + a1) + (b0 + b1);
+      }
+      PROF_MARK7(5);
+      {
+        const uint32_t(&pp0)[32] = *reinterpret_cast<const uint32_t(*)[32]>(&s[0]);
+        const uint32_t(&pp1)[32] = *reinterpret_cast<const uint32_t(*)[32]>(&s[32]);
+        tmem_st_32x32(p_tmem, pp0);
+        tmem_st_32x32(p_tmem + 32, pp1);
+        tmem_wait_st();
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&p_full[b]);
+      PROF_MARK7(6);
+    }
+    if (prof) {
+      for (int k = 0; k < 7; ++k) p.prof[k] = tacc[k];
+      p.prof[7] = (nt + 1) / 2;
+    }
+    // ---- epilogue: O / l -> bf16 -> global [b, f, head, grp*D/2 ...]
+    if (nt > 0) {
+      const int jl = nt - 1;
+      if ((jl & 1) != grp) mbar_wait(&m_ready[(jl & 1) * 4 + quad], (jl >> 1) & 1);
+      const float m_final = mref[(jl & 1) * kA7BM + row];
+      if (m_final != m_local) l_part *= exp2_approx(m_local - m_final);
+      lsum_x[grp * kA7BM + row] = l_part;
+      softmax_pair_barrier7();
+      const float l_sum = l_part + lsum_x[(grp ^ 1) * kA7BM + row];
+      mbar_wait(&pv_done[jl & 1], (jl >> 1) & 1);
+      tc_fence_after();
+      const float inv_l = 1.0f / l_sum;
+      const uint32_t o_tmem = o_all + grp * (D / 2);
+      __nv_bfloat16* dst = p.O + batch * p.o_stride_b + static_cast<int64_t>(f) * p.o_stride_s + head * p.o_stride_h +
+                           grp * (D / 2);
+#pragma unroll 1
+      for (int c = 0; c < D / 64; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(o_tmem + c * 32, r);
+        tmem_wait_ld();
+        if (f < p.Sq) {
+#pragma unroll
+          for (int i = 0; i < 32; i += 8) {
+            uint4 o;
+            o.x = pack_bf16x2(__uint_as_float(r[i]) * inv_l, __uint_as_float(r[i + 1]) * inv_l);
+            o.y = pack_bf16x2(__uint_as_float(r[i + 2]) * inv_l, __uint_as_float(r[i + 3]) * inv_l);
+            o.z = pack_bf16x2(__uint_as_float(r[i + 4]) * inv_l, __uint_as_float(r[i + 5]) * inv_l);
+            o.w = pack_bf16x2(__uint_as_float(r[i + 6]) * inv_l, __uint_as_float(r[i + 7]) * inv_l);
+            *reinterpret_cast<uint4*>(dst + c * 32 + i) = o;
+          }
+        }
+      }
+    }
+  }
+
+  __syncwarp();
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+  }
+}
+
+int make_bsnh_map(CUtensorMap* tm, const void* base, int B, int S, int H, int D, int64_t sb, int64_t ss, int64_t sh,
+                  int rows);
+
+template <int D>
+static int launch_attention7(const void* Q, const void* K, const void* V, const Attn7Params& p, int B, int Sq, int Sk,
+                             int H, const int64_t* qs, const int64_t* ks, const int64_t* vs, cudaStream_t stream) {
+  using Cfg = Attn7Cfg<D>;
+  static_assert(Cfg::kStages >= 3, "KV ring needs at least three stages");
+  CUtensorMap tmQ, tmK, tmV;
+  int rc = make_bsnh_map(&tmQ, Q, B, Sq, H, D, qs[0], qs[1], qs[2], kA7BM);
+  if (rc != B200_OK) return rc;
+  rc = make_bsnh_map(&tmK, K, B, Sk, H, D, ks[0], ks[1], ks[2], kA7BN);
+  if (rc != B200_OK) return rc;
+  rc = make_bsnh_map(&tmV, V, B, Sk, H, D, vs[0], vs[1], vs[2], kA7BN);
+  if (rc != B200_OK) return rc;
+  auto kern = attention_fwd7_kernel<D>;
+  B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+  dim3 grid(p.num_q_tiles, H, B);
+  kern<<<grid, kA7Threads, Cfg::kSmemBytes, stream>>>(tmQ, tmK, tmV, p);
+  B200_CUDA_CHECK(cudaGetLastError());
+  launch_counter().fetch_add(1);
+  return B200_OK;
+}
+
+extern long long* g_attn_prof;
+
+int attention_fwd7_dispatch(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
+                            const int64_t* strides, float scale, int causal, cudaStream_t stream) {
+  Attn7Params p = {};
+  p.O = reinterpret_cast<__nv_bfloat16*>(O);
+  p.Sq = Sq;
+  p.Sk = Sk;
+  p.o_stride_b = strides[9];
+  p.o_stride_s = strides[10];
+  p.o_stride_h = strides[11];
+  p.scale_log2 = scale * 1.4426950408889634f;
+  p.causal = causal ? 1 : 0;
+  p.num_q_tiles = (Sq + kA7BM - 1) / kA7BM;
+  p.prof = g_attn_prof;
+  if (D == 64) return launch_attention7<64>(Q, K, V, p, B, Sq, Sk, H, strides, strides + 3, strides + 6, stream);
+  return launch_attention7<128>(Q, K, V, p, B, Sq, Sk, H, strides, strides + 3, strides + 6, stream);
+}
+
+}  // namespace b200

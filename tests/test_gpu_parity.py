@@ -197,14 +197,35 @@ def test_attention_against_golden(ljs, d, causal):
                                    (2, 100, 1000, 2, 64), (1, 1024, 1024, 4, 128), (1, 384, 640, 2, 128),
                                    (1, 1300, 1300, 1, 64)])
 @pytest.mark.parametrize("causal", [False, True])
-@pytest.mark.parametrize("variant", [1, 2, 3, 4, 5, 6])
+@pytest.mark.parametrize("variant", [1, 2, 3, 4, 5, 6, 7, 8, 9])
 def test_attention_ragged_shapes(ljs, shape, causal, variant):
     ljs.capi.set_attention_variant(variant)      # 1 = one query tile per CTA, 2 / 3 = two tiles (128- / 64-key KV tiles)
     B, Sq, Sk, H, D = shape
+    if variant == 9 and D != 128:
+        pytest.skip("variant 9 (CTA pairs) is head dim 128 only")
     q = rm.synthetic((B, Sq, H, D), 40).to(torch.bfloat16)
     k = rm.synthetic((B, Sk, H, D), 41).to(torch.bfloat16)
     v = rm.synthetic((B, Sk, H, D), 42).to(torch.bfloat16)
     o = ljs.capi.attention_fwd(_dev(q), _dev(k), _dev(v), causal=causal).cpu()
+    torch.testing.assert_close(o.float(), rm.attention_core(q, k, v, causal=causal).float(), **BF16_TOL)
+
+
+@pytest.mark.parametrize("variant", [2, 5, 7, 8, 9])
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("ramp_top", [24.0, 2.0, 1.0])   # every row rescales in every tile / 90-99 % of rows / alternate tiles
+def test_attention_growing_row_max(ljs, variant, causal, ramp_top):
+    """Logits that grow along the key axis: the running max rises by more than the lazy-rescale threshold (2^8) several
+    times per row, in even and in odd KV tiles, so O is rescaled in TMEM by either softmax group of variant 7."""
+    ljs.capi.set_attention_variant(variant)
+    B, S, H, D = 1, 1024, 2, 128
+    q = rm.synthetic((B, S, H, D), 60).to(torch.bfloat16)
+    k = rm.synthetic((B, S, H, D), 61).to(torch.bfloat16)
+    v = rm.synthetic((B, S, H, D), 62).to(torch.bfloat16)
+    ramp = torch.linspace(0.0, ramp_top, S).view(1, S, 1, 1)
+    q = (q.float().abs() + 0.5).to(torch.bfloat16)                     # positive queries ...
+    k = (k.float().abs() * ramp + ramp).to(torch.bfloat16)             # ... against keys whose size grows with position
+    o = ljs.capi.attention_fwd(_dev(q), _dev(k), _dev(v), causal=causal).cpu()
+    assert torch.isfinite(o.float()).all()
     torch.testing.assert_close(o.float(), rm.attention_core(q, k, v, causal=causal).float(), **BF16_TOL)
 
 

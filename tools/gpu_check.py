@@ -139,6 +139,8 @@ def main():
                                           (1, 128, 256, 1, 128, False), (2, 256, 512, 2, 128, False),
                                           (1, 384, 384, 2, 64, True), (1, 200, 333, 2, 128, False),
                                           (1, 1024, 1024, 2, 128, True)]:
+            if args.g == 9 and D != 128:
+                continue
             q = rm.synthetic((B, Sq, H, D), 1).to(torch.bfloat16)
             k = rm.synthetic((B, Sk, H, D), 2).to(torch.bfloat16)
             v = rm.synthetic((B, Sk, H, D), 3).to(torch.bfloat16)
@@ -240,14 +242,18 @@ def main():
         torch.cuda.synchronize()
         lib.b200_attention_set_profile_buffer(None)
         t = buf.cpu().tolist()
-        if args.g == 5:
+        if args.g in (5, 7, 9):
             nt = max(t[7], 1)
             names5 = ["wait s_full", "tmem ld S + s_free", "mask + half max", "xchg barrier", "decide / rescale / P-buffer wait",
                       "exp", "tmem st P + arrive"]
-            print(f"  v5 softmax warp 4 of block (0,0,0): {nt} KV tiles, cycles per tile:")
+            if args.g in (7, 9):
+                names5[2:4] = ["mask + row max", "wait reference max of tile j-1"]
+            print(f"  v{args.g} softmax warp 4 of block (0,0,0): {nt} KV tiles of this warp, cycles per tile:")
             for n, c in zip(names5, t[:7]):
                 print(f"    {n:34s} {c / nt:8.0f}")
             print(f"    {'total':34s} {sum(t[:7]) / nt:8.0f}")
+            if args.g == 9:
+                print(f"    {'epilogues (per own tile)':34s} {t[11] / nt:8.0f}")
             print(f"  MMA warp: {t[8] / nt:.0f} cycles per tile in the loop, {t[9] / nt:.0f} issuing, {t[10] / nt:.1f} polls per tile",
                   flush=True)
             print("RESULT PASS")
@@ -277,11 +283,50 @@ def main():
         for _ in range(3):
             capi.attention_fwd(q, k, v)
         torch.cuda.synchronize()
+    elif args.what == "attn_clock":
+        # sustained run of each variant (and cuDNN SDPA) with NVML clock / power sampling: converts the measured time
+        # into SM cycles per (CTA, KV tile), the unit the clock64 phase profiles are in
+        sys.path.insert(0, ROOT)
+        from bench import ClockSampler
+        B, S, H, D = 8, 4096, 32, 128
+        q, k, v = (torch.randn(B, S, H, D, device="cuda").to(torch.bfloat16) for _ in range(3))
+        o = torch.empty_like(q)
+        qt, kt, vt = (t.transpose(1, 2) for t in (q, k, v))
+        fl = 4.0 * B * H * S * S * D
+        ctas = B * H * (S // 128)
+        waves = -(-ctas // torch.cuda.get_device_properties(0).multi_processor_count)
+        for name in ["v8", "v9", "sdpa", "v9", "v8", "sdpa"]:
+            if name == "sdpa":
+                fn = lambda: torch.nn.functional.scaled_dot_product_attention(qt, kt, vt)
+            else:
+                capi.set_attention_variant(int(name[1:]))
+                fn = lambda: capi.attention_fwd(q, k, v, out=o)
+            for _ in range(20):
+                fn()
+            torch.cuda.synchronize()
+            cs = ClockSampler(0)
+            cs.start()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            iters = 400
+            e0.record()
+            for _ in range(iters):
+                fn()
+            e1.record()
+            torch.cuda.synchronize()
+            c = cs.stop()
+            ms = e0.elapsed_time(e1) / iters
+            mhz = c.get("sm_mhz") or 0
+            cyc = ms * 1e-3 * mhz * 1e6 / (waves * (S // 128)) if name != "sdpa" else float("nan")
+            print(f"  {name:5s} {ms:.3f} ms {fl / ms / 1e9:7.1f} TFLOP/s  sm {mhz} MHz (min {c.get('sm_min_mhz')}) "
+                  f"power max {c.get('power_w_max')} W {c.get('reasons')}  -> {cyc:.0f} cycles per CTA-tile", flush=True)
+        capi.set_attention_variant(0)
     elif args.what == "attn_time":
         if args.g:
             capi.set_attention_variant(args.g)
         for (B, S, H, D, causal) in [(8, 4096, 32, 128, False), (8, 4096, 32, 128, True), (4, 8192, 32, 128, True),
                                      (8, 4096, 32, 64, False)]:
+            if args.g == 9 and D != 128:
+                continue
             q, k, v = (torch.randn(B, S, H, D, device="cuda").to(torch.bfloat16) for _ in range(3))
             o = torch.empty_like(q)
             ms = time_fn(lambda: capi.attention_fwd(q, k, v, causal=causal, out=o), iters=5, warmup=2)
