@@ -35,6 +35,14 @@ namespace b200 {
 #define B200_ATTN_PROFILE 0   // 1: per-phase clock64 totals of one warp into Params::prof (tools/gpu_check.py attn_phases)
 #endif
 
+#ifndef B200_ATTN9_QK_FIRST
+#define B200_ATTN9_QK_FIRST 1   // MMA issue order when both are ready: Q.K^T (what the softmax waits for next) before P.V
+#endif
+
+#ifndef B200_ATTN9_POLY
+#define B200_ATTN9_POLY 0       // n > 0: every (1 << n)-th pair of exp2 goes to a degree-3 polynomial on the FMA pipe
+#endif
+
 constexpr int kA9BM = 128;      // query rows per CTA (256 per pair)
 constexpr int kA9BN = 128;      // keys per KV tile
 constexpr int kA9Threads = 384;
@@ -236,6 +244,76 @@ attention_fwd9_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     while (pv_ok) {
       bool progressed = false;
       if (mprof) ++m_polls;
+#if B200_ATTN9_QK_FIRST
+      // ---- S[T & 1] = Q . K_j^T, up to two tiles ahead of the softmax
+      if (qk_ok) {
+        const int T = qk.T0 + qk_j, b = T & 1;
+        const int i = 2 * qk.T0 + (qk_j == 0 ? 0 : 2 * qk_j - 1), st = i % Cfg::kStages;                      // K_j
+        const uint32_t ph = (i / Cfg::kStages) & 1;
+        const bool q_ok = qk_j > 0 || mbar_test_wait(q_full, qk.s & 1);
+        const bool s_ok = (T < 2) || mbar_test_wait(&s_free[b], ((T - 2) >> 1) & 1);
+        if (q_ok && s_ok && mbar_test_wait(&kv_full[st], ph)) {
+          tc_fence_after();
+          const bool last = qk_j + 1 == qk.nt;
+          const long long ti = mprof ? clock64() : 0;
+          if (elect_one()) {
+            const uint64_t kd = desc_advance(k_desc0, st * Cfg::kKVBytes);
+            const uint32_t s_tmem = tmem_base + Cfg::kSCol + b * 128;
+            mma_bf16_ss_cg2_c<false>(s_tmem, q_desc0, kd, idesc_qk);
+#pragma unroll
+            for (int kk = 1; kk < D / 16; ++kk) {
+              // 64-wide chunk kk/4 of the head dim: 128 Q rows x 128 B per chunk, 64 key rows x 128 B per chunk
+              const uint32_t oq = (kk >> 2) * (kA9BM * 128) + (kk & 3) * 32;
+              const uint32_t ok = (kk >> 2) * (64 * 128) + (kk & 3) * 32;
+              mma_bf16_ss_cg2_c<true>(s_tmem, desc_advance(q_desc0, oq), desc_advance(kd, ok), idesc_qk);
+            }
+            mma_commit_cg2(&s_full[b], 0x3);
+            mma_commit_cg2(&kv_empty[st], 0x3);
+            if (last) mma_commit_cg2(q_free, 0x3);
+          }
+          __syncwarp();
+          if (mprof) m_issue += clock64() - ti;
+          if (++qk_j == qk.nt) {
+            qk_ok = qk.next();
+            qk_j = 0;
+          }
+          progressed = true;
+        }
+      }
+      // ---- O (+)= P(T) . V : first, it is what the softmax two tiles later and the epilogue wait for
+      const int Tpv = pv.T0 + pv_j;
+      const int Tqk = qk_ok ? qk.T0 + qk_j : 0x7fffffff;
+      if (Tpv < Tqk) {
+        const int b = Tpv & 1;
+        const int i = 2 * pv.T0 + ((pv_j + 1 < pv.nt) ? 2 * pv_j + 2 : 2 * pv_j + 1), st = i % Cfg::kStages;   // V_j
+        const uint32_t ph = (i / Cfg::kStages) & 1;
+        // the first P.V of an item overwrites O: the epilogue of the previous item must have read it
+        const bool o_ok = pv_j > 0 || pv.s == 0 || mbar_test_wait(o_free, (pv.s - 1) & 1);
+        if (o_ok && mbar_test_wait(&p_full[b], (Tpv >> 1) & 1) && mbar_test_wait(&kv_full[st], ph)) {
+          tc_fence_after();
+          const long long ti = mprof ? clock64() : 0;
+          if (elect_one()) {
+            const uint64_t vd = desc_advance(v_desc0, st * Cfg::kKVBytes);
+            const uint32_t p_tmem = tmem_base + Cfg::kPCol + b * 64;     // 16 keys = 8 columns per MMA
+            const uint32_t o_tmem = tmem_base + Cfg::kOCol;
+            if (pv_j == 0) mma_bf16_ts_cg2_c<false>(o_tmem, p_tmem, vd, idesc_pv);
+            else mma_bf16_ts_cg2_c<true>(o_tmem, p_tmem, vd, idesc_pv);
+#pragma unroll
+            for (int kk = 1; kk < kA9BN / 16; ++kk)
+              mma_bf16_ts_cg2_c<true>(o_tmem, p_tmem + kk * 8, desc_advance(vd, kk * (16 * 128)), idesc_pv);
+            mma_commit_cg2(&pv_done[b], 0x3);
+            mma_commit_cg2(&kv_empty[st], 0x3);
+          }
+          __syncwarp();
+          if (mprof) m_issue += clock64() - ti;
+          if (++pv_j == pv.nt) {
+            pv_ok = pv.next();
+            pv_j = 0;
+          }
+          progressed = true;
+        }
+      }
+#else
       // ---- O (+)= P(T) . V : first, it is what the softmax two tiles later and the epilogue wait for
       const int Tpv = pv.T0 + pv_j;
       const int Tqk = qk_ok ? qk.T0 + qk_j : 0x7fffffff;
@@ -304,6 +382,7 @@ attention_fwd9_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
           progressed = true;
         }
       }
+#endif
 #if B200_WATCHDOG
       if (progressed) {
         idle = 0;
@@ -434,12 +513,43 @@ attention_fwd9_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         // p = exp2(s * scale_log2 - m_used) -> bf16 pairs in place -> TMEM P[b]
         const uint64_t negm2 = pack_f32x2(-m_used, -m_used);
         uint64_t sum2[2] = {0ull, 0ull};
+#if B200_ATTN9_POLY
+        // 2^x = 2^n * 2^f, n = round(x) by the magic-number add, f in [-0.5, 0.5], 2^f by a degree-3 polynomial (max
+        // relative error 1.0e-4, inside bf16's 2^-9), n added into the exponent bits; masked tiles keep MUFU throughout
+        const bool poly_ok = !__any_sync(0xffffffffu, need_mask);
+        const uint64_t magic2 = pack_f32x2(12582912.0f, 12582912.0f);          // 1.5 * 2^23
+        const uint64_t nmagic2 = pack_f32x2(-12582912.0f, -12582912.0f);
+        const uint64_t neg1 = pack_f32x2(-1.0f, -1.0f);
+        const uint64_t c3 = pack_f32x2(0.05592203512787819f, 0.05592203512787819f);
+        const uint64_t c2 = pack_f32x2(0.24264007806777954f, 0.24264007806777954f);
+        const uint64_t c1 = pack_f32x2(0.6931210160255432f, 0.6931210160255432f);
+        const uint64_t c0 = pack_f32x2(0.9999244809150696f, 0.9999244809150696f);
+#endif
 #pragma unroll
         for (int i = 0; i < 64; ++i) {
           const uint64_t x2 = fma_f32x2(pack_f32x2(__uint_as_float(s[2 * i]), __uint_as_float(s[2 * i + 1])), scale2, negm2);
           float x0, x1;
           unpack_f32x2(x2, x0, x1);
-          const float p0 = exp2_approx(x0), p1 = exp2_approx(x1);
+          float p0, p1;
+#if B200_ATTN9_POLY
+          if ((i & ((1 << B200_ATTN9_POLY) - 1)) == ((1 << B200_ATTN9_POLY) - 1) && poly_ok) {
+            const uint64_t xc = pack_f32x2(fmaxf(x0, -125.0f), fmaxf(x1, -125.0f));
+            const uint64_t t2 = add_f32x2(xc, magic2);                         // n in the low mantissa bits
+            const uint64_t f2 = fma_f32x2(add_f32x2(t2, nmagic2), neg1, xc);   // f = x - n
+            uint64_t q2 = fma_f32x2(c3, f2, c2);
+            q2 = fma_f32x2(q2, f2, c1);
+            q2 = fma_f32x2(q2, f2, c0);
+            float q0, q1, t0f, t1f;
+            unpack_f32x2(q2, q0, q1);
+            unpack_f32x2(t2, t0f, t1f);
+            p0 = __int_as_float(__float_as_int(q0) + (__float_as_int(t0f) << 23));
+            p1 = __int_as_float(__float_as_int(q1) + (__float_as_int(t1f) << 23));
+          } else
+#endif
+          {
+            p0 = exp2_approx(x0);
+            p1 = exp2_approx(x1);
+          }
           sum2[i & 1] = add_f32x2(sum2[i & 1], pack_f32x2(p0, p1));
           s[i] = pack_bf16x2(p0, p1);            // keys (2i, 2i+1): low half = even key
         }

@@ -372,6 +372,7 @@ def test_host_buffer_ffn_step_matches_oracle(ljs):
     cfg = dict(batch=2, seq=1024, d_model=512, d_ff=2048, parallelism="tp")
     bench = layers.FFNBench(cfg, "gelu_tanh", rank=0, world=1, dev=torch.device("cuda", 0))
     y_host = bench.step_e2e()
+    bench.e2e_drain()
     torch.cuda.synchronize()
     x = rm.synthetic((2048, 512), 0)
     w1, b1 = rm.synthetic((512, 2048), 1, "weight"), rm.synthetic((2048,), 2, "bias")
@@ -382,3 +383,12 @@ def test_host_buffer_ffn_step_matches_oracle(ljs):
     y_dev = bench.step_resident()
     torch.cuda.synchronize()
     torch.testing.assert_close(y_dev.cpu().float(), y_host.float(), rtol=0, atol=0)
+    # streaming: back-to-back calls alternate between two sets of staging buffers and overlap; every result is complete
+    # after the drain and identical
+    first = y_host.clone()
+    outs = [bench.step_e2e() for _ in range(5)]
+    bench.e2e_drain()
+    torch.cuda.synchronize()
+    assert outs[0].data_ptr() != outs[1].data_ptr() and outs[0].data_ptr() == outs[2].data_ptr()
+    for o in outs[-2:]:
+        assert torch.equal(o, first)

@@ -320,6 +320,33 @@ def main():
             print(f"  {name:5s} {ms:.3f} ms {fl / ms / 1e9:7.1f} TFLOP/s  sm {mhz} MHz (min {c.get('sm_min_mhz')}) "
                   f"power max {c.get('power_w_max')} W {c.get('reasons')}  -> {cyc:.0f} cycles per CTA-tile", flush=True)
         capi.set_attention_variant(0)
+    elif args.what == "attn_quick":
+        # one line per call, for A/B runs of library variants: burst (5 iterations) non-causal / causal and a sustained
+        # run (300 launches) with the NVML clock, all at B8 S4096 H32 D128
+        sys.path.insert(0, ROOT)
+        from bench import ClockSampler
+        if args.g:
+            capi.set_attention_variant(args.g)
+        B, S, H, D = 8, 4096, 32, 128
+        q, k, v = (torch.randn(B, S, H, D, device="cuda").to(torch.bfloat16) for _ in range(3))
+        o = torch.empty_like(q)
+        out = []
+        for causal in (False, True):
+            ms = time_fn(lambda: capi.attention_fwd(q, k, v, causal=causal, out=o), iters=5, warmup=2)
+            fl = (2.0 * B * H * S * (S + 1) * D) if causal else 4.0 * B * H * S * S * D
+            out.append(fl / ms / 1e9)
+        cs = ClockSampler(0)
+        cs.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(300):
+            capi.attention_fwd(q, k, v, out=o)
+        e1.record()
+        torch.cuda.synchronize()
+        c = cs.stop()
+        ms = e0.elapsed_time(e1) / 300
+        print(f"  QUICK g={args.g} burst {out[0]:.1f} / causal {out[1]:.1f}  sustained {4.0 * B * H * S * S * D / ms / 1e9:.1f} TFLOP/s "
+              f"@ {c.get('sm_mhz')} MHz", flush=True)
     elif args.what == "attn_time":
         if args.g:
             capi.set_attention_variant(args.g)
