@@ -477,16 +477,16 @@ class FFNBench:
         self.copy_in = torch.cuda.Stream(device=dev)
         self.copy_out = torch.cuda.Stream(device=dev)
         self._events = []
-        # single-GPU streaming path: two sets of staging buffers (by step parity) so that the uploads of step i+1 and the
-        # downloads of step i-1 run under the GEMMs of step i; 2 token chunks per step keep both GEMMs at full waves
-        self.e2e_chunks = 2
+        # streaming host-buffer path: two sets of staging buffers (by step parity) so that the uploads of step i+1 and the
+        # downloads of step i-1 run under the GEMMs of step i; on one GPU 2 token chunks per step keep both GEMMs at full
+        # waves, on several GPUs a step is one chunk (the layer has its own chunking for the collective)
+        self.e2e_chunks = 2 if world == 1 else 1
         self._e2e_step = 0
-        if world == 1:
-            self._x_stages = [self.x_stage, torch.empty_like(self.x)]
-            self._y_devs = [torch.empty((self.T_out, d), dtype=torch.bfloat16, device=dev) for _ in range(2)]
-            self._y_hosts = [self.y_host, torch.empty((self.T_out, d), dtype=torch.bfloat16).pin_memory()]
-            mk = lambda: [[torch.cuda.Event() for _ in range(self.e2e_chunks)] for _ in range(2)]
-            self._in_ev, self._xfree_ev, self._out_ev, self._ycopied_ev = mk(), mk(), mk(), mk()
+        self._x_stages = [self.x_stage, torch.empty_like(self.x)]
+        self._y_devs = [torch.empty((self.T_out, d), dtype=torch.bfloat16, device=dev) for _ in range(2)]
+        self._y_hosts = [self.y_host, torch.empty((self.T_out, d), dtype=torch.bfloat16).pin_memory()]
+        mk = lambda: [[torch.cuda.Event() for _ in range(self.e2e_chunks)] for _ in range(2)]
+        self._in_ev, self._xfree_ev, self._out_ev, self._ycopied_ev = mk(), mk(), mk(), mk()
 
     def parallelism_name(self):
         if self.mode == "single":
@@ -526,26 +526,35 @@ class FFNBench:
         GEMMs of chunk c and the D2H copy of chunk c-1 overlap (PCIe is full duplex)."""
         main = torch.cuda.current_stream(self.dev)
         if self.world > 1:
-            self.copy_in.wait_stream(main)
+            # Several GPUs: the same streaming scheme with one chunk per step.  In TP mode x is replicated over the model
+            # axis: every rank uploads only ITS 1/W of the rows over PCIe and the ranks all-gather the rest over NVLink
+            # (W x 134 MB of host reads would be PCIe-bound).  The layer writes its own output buffer, so the result is
+            # moved to this step's staging buffer (a device copy) before the download starts.
+            par = self._e2e_step & 1
+            self._e2e_step += 1
+            x_stage, y_dev, y_host = self._x_stages[par], self._y_devs[par], self._y_hosts[par]
             if self.mode == "tp":
-                # x is replicated over the model axis: every rank uploads only ITS 1/W of the rows over PCIe
-                # and the ranks all-gather the rest over NVLink (8 x 134 MB of host reads would be PCIe-bound)
                 rows = self.T // self.world
                 sl = slice(self.rank * rows, (self.rank + 1) * rows)
-                with torch.cuda.stream(self.copy_in):
-                    self.x_stage[sl].copy_(self.x_host[sl], non_blocking=True)
-                main.wait_stream(self.copy_in)
-                self._dist.all_gather_into_tensor(self.x_stage, self.x_stage[sl])
             else:
-                with torch.cuda.stream(self.copy_in):
-                    self.x_stage.copy_(self.x_host, non_blocking=True)
-                main.wait_stream(self.copy_in)
-            y = self.layer.forward(self.x_stage)
-            self.copy_out.wait_stream(main)
+                sl = slice(0, self.T_in)
+            with torch.cuda.stream(self.copy_in):
+                self.copy_in.wait_event(self._xfree_ev[par][0])      # the forward of two calls ago has read x_stage
+                x_stage[sl].copy_(self.x_host[sl] if self.mode == "tp" else self.x_host, non_blocking=True)
+                self._in_ev[par][0].record(self.copy_in)
+            main.wait_event(self._in_ev[par][0])
+            if self.mode == "tp":
+                self._dist.all_gather_into_tensor(x_stage, x_stage[sl])
+            y = self.layer.forward(x_stage)
+            self._xfree_ev[par][0].record(main)
+            main.wait_event(self._ycopied_ev[par][0])                # the download of two calls ago has read y_dev
+            y_dev.copy_(y, non_blocking=True)
+            self._out_ev[par][0].record(main)
             with torch.cuda.stream(self.copy_out):
-                self.y_host.copy_(y, non_blocking=True)
-            main.wait_stream(self.copy_out)
-            return self.y_host
+                self.copy_out.wait_event(self._out_ev[par][0])
+                y_host.copy_(y_dev, non_blocking=True)
+                self._ycopied_ev[par][0].record(self.copy_out)
+            return y_host
         # One GPU: a streaming call.  Step i uses staging set i % 2; within a step the tokens go through in chunks.  Every
         # dependency is an event on the buffer concerned (no stream-wide joins), so consecutive calls overlap: PCIe is
         # full duplex and the copy engines run beside the GEMMs.  The returned pinned buffer is complete once

@@ -108,6 +108,21 @@ def main():
     good = bool(((got - ref).abs() <= 2e-2 * ref.abs() + 2e-2).all())
     print(f"[rank {rank}] nn.ffn (NamedSharding, NCCL reduce-scatter): {'OK' if good else 'FAIL'}", flush=True)
     ok &= good
+    # the streaming host-buffer step bench.py times as `e2e`, in both shardings: several overlapping calls, every returned
+    # pinned buffer against the oracle rows this rank owns
+    for mode in ("tp", "fsdp"):
+        cfg = dict(batch=2, seq=T // 2, d_model=d, d_ff=f, parallelism=mode)
+        fb = layers.FFNBench(cfg, "gelu_tanh", rank, world, dev)
+        outs = [fb.step_e2e() for _ in range(5)]
+        fb.e2e_drain()
+        torch.cuda.synchronize()
+        blk = T // world
+        ref = want[rank * blk:(rank + 1) * blk]
+        good = all(bool(((o.float() - ref).abs() <= 2e-2 * ref.abs() + 2e-2).all()) for o in outs[-2:])
+        good &= outs[0].data_ptr() != outs[1].data_ptr()
+        print(f"[rank {rank}] streaming host-buffer step ({mode}, {fb.parallelism_name()}): {'OK' if good else 'FAIL'}", flush=True)
+        ok &= good
+        del fb
     t = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
     if rank == 0:
