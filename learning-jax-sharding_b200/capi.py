@@ -142,6 +142,11 @@ def set_gemm_group_m(group_m: int = 0):
     _check(load().b200_gemm_set_group_m(group_m), "b200_gemm_set_group_m")
 
 
+def set_gemm_k_serpentine(mode: int = -1):
+    """-1 = library heuristic, 0 / 1 = every other tile of a CTA walks K downwards off / on. Tuning hook."""
+    _check(load().b200_gemm_set_k_serpentine(mode), "b200_gemm_set_k_serpentine")
+
+
 def set_attention_variant(variant: int = 0):
     """0 = library heuristic, 1 = one 128-row query tile per CTA, 2 = two tiles per CTA (ping-pong)."""
     _check(load().b200_attention_set_variant(variant), "b200_attention_set_variant")

@@ -56,6 +56,8 @@ struct GemmParams {
   void* const* c_block_ptrs;
   int m_rows_per_block, m_block_rot, m_num_blocks;
   int num_stages;   // smem ring depth actually used (<= Cfg::kStages); tuning experiments only
+  int k_serpentine; // 1: every other tile of a CTA walks K downwards, so a wave starts on the K range the previous wave
+                    // has just left in L2 (the panels of one wave exceed L2 when K is large)
 };
 
 __device__ __forceinline__ float gelu_tanh_f(float x) {
@@ -146,6 +148,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     uint32_t phase = 0;
     // (L2 eviction hints were tried and removed: evict_first on B made the B tiles shared by neighbouring CTAs
     //  miss, evict_last on A did not keep a 67 MB panel group resident -- profiles/r01_l2_hint_experiment.md.)
+    bool k_down = false;
     for (int tile = worker; tile < num_tiles; tile += num_workers) {
       int m_blk, n_blk;
       tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, m_blk, n_blk);
@@ -159,7 +162,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         mbar_wait(&empty_bar[stage], phase ^ 1);
         uint8_t* sa = smem + stage * Cfg::kStageBytes;
         uint8_t* sb = sa + Cfg::kABytes;
-        const int k0 = kb * kBK;
+        const int k0 = (k_down ? num_kb - 1 - kb : kb) * kBK;   // the MMA side only sees ring slots: any K order works
         if (elect_one()) {
         if (G == 1) {
           mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
@@ -187,6 +190,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         __syncwarp();
         if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
       }
+      if (p.k_serpentine) k_down = !k_down;
     }
   } else if (warp == 1 && leader) {
     // ===================== MMA issuer (leader CTA only) =====================
@@ -379,6 +383,7 @@ static int g_force_cta_group = 0;   // 0 = heuristic; 1 / 2 force (set through b
 static int g_force_bn = 0;
 static int g_group_m = 0;   // 0 = heuristic below
 static int g_max_stages = 0;   // 0 = all the stages that fit
+static int g_k_serpentine = -1;   // -1 = heuristic, 0 / 1 force
 
 template <int BN, int G, bool kBKmajor>
 static int launch_gemm(const void* A, int64_t lda, const void* B, int64_t ldb, const GemmParams& p0,
@@ -394,6 +399,7 @@ static int launch_gemm(const void* A, int64_t lda, const void* B, int64_t ldb, c
   if (G == 2 && stages > 4) stages = 4;
   if (g_max_stages > 0 && g_max_stages < stages) stages = g_max_stages;
   p.num_stages = stages;
+  p.k_serpentine = g_k_serpentine >= 0 ? g_k_serpentine : 0;
   if (g_group_m > 0) {
     p.group_m = g_group_m;
   } else {
@@ -474,6 +480,12 @@ extern "C" int b200_gemm_set_tuning(int cta_group, int block_n) {
 extern "C" int b200_gemm_set_max_stages(int stages) {
   if (stages < 0 || stages > 8) return fail(B200_ERR_INVALID_ARGUMENT, "stages must be in [0, 8]");
   g_max_stages = stages;
+  return B200_OK;
+}
+
+extern "C" int b200_gemm_set_k_serpentine(int mode) {
+  if (mode < -1 || mode > 1) return fail(B200_ERR_INVALID_ARGUMENT, "k_serpentine must be -1 (auto), 0 or 1");
+  g_k_serpentine = mode;
   return B200_OK;
 }
 

@@ -268,16 +268,46 @@ def main():
         print(f"    {'total':18s} {sum(t[:6]) / nt:8.0f}", flush=True)
     elif args.what == "gemm_traffic":
         # run under: ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum -k regex:gemm_bf16
-        for (M, N, K, gms) in [(16384, 16384, 4096, (4, 8, 16, 32)), (16384, 4096, 16384, (2, 4, 8, 16))]:
+        # launches, in order: for each of the two FFN GEMM shapes, (group_m, k_serpentine) combinations
+        for (M, N, K, combos) in [(16384, 16384, 4096, ((16, 0), (16, 1), (8, 1), (32, 1))),
+                                  (16384, 4096, 16384, ((8, 0), (8, 1), (4, 1), (16, 1), (64, 1)))]:
             a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
             b = torch.randn(K, N, device="cuda").to(torch.bfloat16)
             out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
-            for gm in gms:
+            for (gm, ks) in combos:
                 capi.set_gemm_group_m(gm)
+                capi.set_gemm_k_serpentine(ks)
                 capi.gemm_bf16(a, b, out=out)
                 torch.cuda.synchronize()
-                print(f"  launched M={M} N={N} K={K} group_m={gm}", flush=True)
+                print(f"  launched M={M} N={N} K={K} group_m={gm} k_serpentine={ks}", flush=True)
         capi.set_gemm_group_m(0)
+        capi.set_gemm_k_serpentine(-1)
+    elif args.what == "gemm_serp":
+        # timing of the two FFN GEMM shapes with / without the serpentine K order, interleaved
+        import statistics
+        for (M, N, K, combos) in [(16384, 16384, 4096, ((16, 0), (16, 1), (8, 1))),
+                                  (16384, 4096, 16384, ((8, 0), (8, 1), (16, 1), (64, 1)))]:
+            a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
+            b = torch.randn(K, N, device="cuda").to(torch.bfloat16)
+            out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+            res = {c: [] for c in combos}
+            for rnd in range(4):
+                for c in combos:
+                    capi.set_gemm_group_m(c[0])
+                    capi.set_gemm_k_serpentine(c[1])
+                    res[c].append(time_fn(lambda: capi.gemm_bf16(a, b, out=out), iters=10, warmup=2))
+            for c in combos:
+                ms = statistics.median(res[c])
+                print(f"  M={M} N={N} K={K} group_m={c[0]} k_serpentine={c[1]}: {ms:.3f} ms {2.0 * M * N * K / ms / 1e9:.1f} TFLOP/s", flush=True)
+            # the serpentine order only permutes the f32 summation: same result within bf16 rounding
+            capi.set_gemm_k_serpentine(0)
+            ref = capi.gemm_bf16(a, b).float()
+            capi.set_gemm_k_serpentine(1)
+            got = capi.gemm_bf16(a, b).float()
+            d = (got - ref).abs().max().item()
+            print(f"  max |serpentine - plain| = {d:.3e} (|C| max {ref.abs().max().item():.1f})", flush=True)
+        capi.set_gemm_group_m(0)
+        capi.set_gemm_k_serpentine(-1)
     elif args.what == "attn_prof":
         q, k, v = (torch.randn(2, 4096, 16, 128, device="cuda").to(torch.bfloat16) for _ in range(3))
         for _ in range(3):
