@@ -142,6 +142,12 @@ def set_gemm_group_m(group_m: int = 0):
     _check(load().b200_gemm_set_group_m(group_m), "b200_gemm_set_group_m")
 
 
+def set_gemm_max_ctas(ctas: int = 0):
+    """Upper bound on the persistent GEMM's grid (0 = one CTA per SM): leaves SMs to a collective kernel that runs
+    beside it.  Tuning hook."""
+    _check(load().b200_gemm_set_max_ctas(ctas), "b200_gemm_set_max_ctas")
+
+
 def set_gemm_k_serpentine(mode: int = -1):
     """-1 = library heuristic, 0 / 1 = every other tile of a CTA walks K downwards off / on. Tuning hook."""
     _check(load().b200_gemm_set_k_serpentine(mode), "b200_gemm_set_k_serpentine")

@@ -384,6 +384,7 @@ static int g_force_bn = 0;
 static int g_group_m = 0;   // 0 = heuristic below
 static int g_max_stages = 0;   // 0 = all the stages that fit
 static int g_k_serpentine = -1;   // -1 = heuristic, 0 / 1 force
+static int g_max_ctas = 0;        // 0 = one CTA per SM; n > 0 leaves SMs free for a collective running beside the GEMM
 
 template <int BN, int G, bool kBKmajor>
 static int launch_gemm(const void* A, int64_t lda, const void* B, int64_t ldb, const GemmParams& p0,
@@ -439,6 +440,7 @@ static int launch_gemm(const void* A, int64_t lda, const void* B, int64_t ldb, c
   const int sms = num_sms();
   const int tiles = p.tiles_m * p.tiles_n;
   int workers = sms / G;
+  if (g_max_ctas > 0 && g_max_ctas / G < workers) workers = g_max_ctas / G > 0 ? g_max_ctas / G : 1;
   if (tiles < workers) workers = tiles;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(workers * G);
@@ -480,6 +482,12 @@ extern "C" int b200_gemm_set_tuning(int cta_group, int block_n) {
 extern "C" int b200_gemm_set_max_stages(int stages) {
   if (stages < 0 || stages > 8) return fail(B200_ERR_INVALID_ARGUMENT, "stages must be in [0, 8]");
   g_max_stages = stages;
+  return B200_OK;
+}
+
+extern "C" int b200_gemm_set_max_ctas(int ctas) {
+  if (ctas < 0 || ctas > 4096) return fail(B200_ERR_INVALID_ARGUMENT, "max_ctas must be in [0, 4096]");
+  g_max_ctas = ctas;
   return B200_OK;
 }
 

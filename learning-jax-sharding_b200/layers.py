@@ -239,9 +239,17 @@ class FsdpFFN:
     """FSDP layout (BASELINE.json case3 config): tokens sharded over 'data' (this rank holds
     x[T/world rows]); W1 [d_model, d_ff] and W2 [d_ff, d_model] are dim0-sharded over 'data'.
     Each weight is all-gathered in `chunks` column chunks on a side stream; the GEMM on column
-    chunk j runs while chunk j+1 (and then W2's chunks) are in flight."""
+    chunk j runs while chunk j+1 (and then W2's chunks) are in flight.
 
-    def __init__(self, w1_shard, b1, w2_shard, b2, act: str, T_local: int, group, chunks: int = 4):
+    `prefetch=True` (default): the gathered-weight buffers are double-buffered by call parity and a forward call also
+    starts the all-gather of W1 for the NEXT call once W2's chunks are queued (FSDP "forward prefetch"), so in a
+    steady stream of calls W1's gather runs under GEMM2 of the call before.  Every call still gathers both weights in
+    full over NVLink -- nothing gathered is kept beyond the call that uses it.  Dependencies are per-buffer events
+    (the side stream never joins the whole main stream).  `gemm_max_ctas` > 0 bounds the persistent GEMM's grid so the
+    collective's CTAs find free SMs beside it (0 = env B200_FSDP_GEMM_CTAS or no bound)."""
+
+    def __init__(self, w1_shard, b1, w2_shard, b2, act: str, T_local: int, group, chunks: int = 4, prefetch: bool = True,
+                 gemm_max_ctas: int = 0):
         import torch.distributed as dist
         self.dist, self.group = dist, group
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
@@ -251,47 +259,77 @@ class FsdpFFN:
         self.F = w1_shard.shape[1]
         self.T = T_local
         self.chunks = chunks
+        self.prefetch = prefetch
+        self.gemm_max_ctas = gemm_max_ctas or int(os.environ.get("B200_FSDP_GEMM_CTAS", "0"))
         dev = w1_shard.device
-        # gathered weights, chunk-major: [chunk][K rows][cols/chunks]
-        self.w1g = torch.empty((chunks, self.d_model, self.F // chunks), dtype=torch.bfloat16, device=dev)
-        self.w2g = torch.empty((chunks, self.F, self.d_model // chunks), dtype=torch.bfloat16, device=dev)
+        nbuf = 2 if prefetch else 1
+        # gathered weights, chunk-major: [buffer][chunk][K rows][cols/chunks]
+        self.w1g = torch.empty((nbuf, chunks, self.d_model, self.F // chunks), dtype=torch.bfloat16, device=dev)
+        self.w2g = torch.empty((nbuf, chunks, self.F, self.d_model // chunks), dtype=torch.bfloat16, device=dev)
         # column-chunked views of the local shards must be contiguous for NCCL: keep a chunk-major copy
         self.w1s_c = w1_shard.reshape(w1_shard.shape[0], chunks, -1).permute(1, 0, 2).contiguous()
         self.w2s_c = w2_shard.reshape(w2_shard.shape[0], chunks, -1).permute(1, 0, 2).contiguous()
         self.h = torch.empty((T_local, self.F), dtype=torch.bfloat16, device=dev)
         self.y = torch.empty((T_local, self.d_model), dtype=torch.bfloat16, device=dev)
         self.comm_stream = torch.cuda.Stream(device=dev)
-        self.ready = [torch.cuda.Event() for _ in range(2 * chunks)]
+        self.ready1 = [[torch.cuda.Event() for _ in range(chunks)] for _ in range(nbuf)]   # W1 chunk gathered
+        self.ready2 = [[torch.cuda.Event() for _ in range(chunks)] for _ in range(nbuf)]   # W2 chunk gathered
+        self.read1 = [torch.cuda.Event() for _ in range(nbuf)]    # the GEMM1s that read w1g[buf] are done
+        self.read2 = [torch.cuda.Event() for _ in range(nbuf)]    # the GEMM2s that read w2g[buf] are done
+        self._call = 0
+        self._w1_inflight = -1        # call index whose W1 gather has already been queued (prefetch)
+
+    def _gather_w1(self, buf):
+        self.comm_stream.wait_event(self.read1[buf])
+        for j in range(self.chunks):
+            self.dist.all_gather_into_tensor(self.w1g[buf, j], self.w1s_c[j], group=self.group)
+            self.ready1[buf][j].record(self.comm_stream)
+
+    def _gather_w2(self, buf):
+        self.comm_stream.wait_event(self.read2[buf])
+        for j in range(self.chunks):
+            self.dist.all_gather_into_tensor(self.w2g[buf, j], self.w2s_c[j], group=self.group)
+            self.ready2[buf][j].record(self.comm_stream)
 
     def forward(self, x: torch.Tensor, record=None) -> torch.Tensor:
         C = self.chunks
         main = torch.cuda.current_stream(x.device)
-        self.comm_stream.wait_stream(main)
+        call = self._call
+        self._call += 1
+        buf = call & 1 if self.prefetch else 0
         with torch.cuda.stream(self.comm_stream):
-            for j in range(C):
-                self.dist.all_gather_into_tensor(self.w1g[j], self.w1s_c[j], group=self.group)
-                self.ready[j].record(self.comm_stream)
-            for j in range(C):
-                self.dist.all_gather_into_tensor(self.w2g[j], self.w2s_c[j], group=self.group)
-                self.ready[C + j].record(self.comm_stream)
+            if not self.prefetch:
+                self.comm_stream.wait_stream(main)
+            if self._w1_inflight != call:
+                self._gather_w1(buf)
+            self._gather_w2(buf)
+            if self.prefetch:
+                self._gather_w1(buf ^ 1)          # for the next call: runs under this call's second GEMM
+                self._w1_inflight = call + 1
+        if self.gemm_max_ctas:
+            capi.set_gemm_max_ctas(self.gemm_max_ctas)
         fc, dc = self.F // C, self.d_model // C
         for j in range(C):
-            main.wait_event(self.ready[j])
+            main.wait_event(self.ready1[buf][j])
             if record is not None:
                 record("start")
             b = self.b1[j * fc:(j + 1) * fc] if self.b1 is not None else None
-            capi.gemm_bf16(x, self.w1g[j], bias=b, epilogue=self.act, out=self.h[:, j * fc:(j + 1) * fc])
+            capi.gemm_bf16(x, self.w1g[buf, j], bias=b, epilogue=self.act, out=self.h[:, j * fc:(j + 1) * fc])
             if record is not None:
                 record("gemm1")
+        self.read1[buf].record(main)
         for j in range(C):
-            main.wait_event(self.ready[C + j])
+            main.wait_event(self.ready2[buf][j])
             if record is not None:
                 record("start")
             b = self.b2[j * dc:(j + 1) * dc] if self.b2 is not None else None
-            capi.gemm_bf16(self.h, self.w2g[j], bias=b, epilogue=capi.EPI_BIAS if b is not None else capi.EPI_NONE,
+            capi.gemm_bf16(self.h, self.w2g[buf, j], bias=b, epilogue=capi.EPI_BIAS if b is not None else capi.EPI_NONE,
                            out=self.y[:, j * dc:(j + 1) * dc])
             if record is not None:
                 record("gemm2")
+        self.read2[buf].record(main)
+        if self.gemm_max_ctas:
+            capi.set_gemm_max_ctas(0)
         return self.y
 
 
@@ -305,7 +343,7 @@ class PeerGatherFFN:
     order is staggered by rank so every source serves one reader at a time."""
 
     def __init__(self, w1_shard, b1, w2_shard, b2, act: str, T_local: int, group, chunks: int = 4, copy_streams: int = 4,
-                 mode: str = "ce", ctas: int = 48):
+                 mode: str = "ce", ctas: int = 48, prefetch: bool = True):
         import torch.distributed as dist
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         W = self.world
@@ -316,6 +354,10 @@ class PeerGatherFFN:
         self.T = T_local
         self.chunks = C = chunks
         self.mode, self.ctas = mode, ctas
+        # prefetch: as in FsdpFFN -- gathered buffers double-buffered by call parity, W1 of the next call pulled under
+        # this call's second GEMM, per-buffer events instead of stream joins
+        self.prefetch = prefetch
+        nbuf = 2 if prefetch else 1
         dev = w1_shard.device
         n1, n2 = w1_shard.numel() * 2, w2_shard.numel() * 2
         self.n1 = n1
@@ -335,19 +377,22 @@ class PeerGatherFFN:
                           for p in range(W)]
         self.src_bases = torch.tensor(self.peer_base, dtype=torch.int64, device=dev)
         # gathered weights, chunk-major: [chunk][W * rows][cols / chunks]
-        self.w1g = torch.empty((C, self.k1 * W, self.F // C), dtype=torch.bfloat16, device=dev)
-        self.w2g = torch.empty((C, self.k2 * W, self.d_model // C), dtype=torch.bfloat16, device=dev)
+        self.w1g = torch.empty((nbuf, C, self.k1 * W, self.F // C), dtype=torch.bfloat16, device=dev)
+        self.w2g = torch.empty((nbuf, C, self.k2 * W, self.d_model // C), dtype=torch.bfloat16, device=dev)
         self.h = torch.empty((T_local, self.F), dtype=torch.bfloat16, device=dev)
         self.y = torch.empty((T_local, self.d_model), dtype=torch.bfloat16, device=dev)
         self.streams = [torch.cuda.Stream(device=dev) for _ in range(copy_streams)]
-        self.ready = [[torch.cuda.Event() for _ in range(copy_streams)] for _ in range(2 * chunks)]
+        self.ready = [[[torch.cuda.Event() for _ in range(copy_streams)] for _ in range(2 * chunks)] for _ in range(nbuf)]
+        self.read = [[torch.cuda.Event() for _ in range(2)] for _ in range(nbuf)]   # [buf][which]: the GEMMs reading it are done
+        self._call = 0
+        self._w1_inflight = -1
         dist.barrier(group=group)
 
-    def _pull(self, which: int, j: int):
-        """Enqueue the pulls of column chunk j of weight `which` (0 = W1, 1 = W2) from every rank."""
+    def _pull(self, which: int, j: int, buf: int):
+        """Enqueue the pulls of column chunk j of weight `which` (0 = W1, 1 = W2) from every rank into buffer `buf`."""
         W, C = self.world, self.chunks
         rows, cols = (self.k1, self.F) if which == 0 else (self.k2, self.d_model)
-        dst = self.w1g if which == 0 else self.w2g
+        dst = self.w1g[buf] if which == 0 else self.w2g[buf]
         blk = rows * (cols // C) * 2                          # bytes of one rank's chunk (contiguous on both sides)
         src_off = (0 if which == 0 else self.n1) + j * blk
         dst0 = dst.data_ptr() + j * W * blk
@@ -359,37 +404,51 @@ class PeerGatherFFN:
                 st = self.streams[i % len(self.streams)]
                 capi.peer_copy2d(dst0 + p * blk, blk, self.peer_base[p] + src_off, blk, blk, 1, st)
         for k, st in enumerate(self.streams):
-            self.ready[which * C + j][k].record(st)
+            self.ready[buf][which * C + j][k].record(st)
+
+    def _pull_weight(self, which: int, buf: int):
+        for st in self.streams:
+            st.wait_event(self.read[buf][which])              # the GEMMs that read this buffer last are done
+        for j in range(self.chunks):
+            self._pull(which, j, buf)
 
     def forward(self, x: torch.Tensor, record=None) -> torch.Tensor:
         C = self.chunks
         main = torch.cuda.current_stream(x.device)
-        for st in self.streams:
-            st.wait_stream(main)                              # the previous step's GEMMs have read w1g / w2g
-        for j in range(C):
-            self._pull(0, j)
-        for j in range(C):
-            self._pull(1, j)
+        call = self._call
+        self._call += 1
+        buf = call & 1 if self.prefetch else 0
+        if not self.prefetch:
+            for st in self.streams:
+                st.wait_stream(main)                          # the previous step's GEMMs have read w1g / w2g
+        if self._w1_inflight != call:
+            self._pull_weight(0, buf)
+        self._pull_weight(1, buf)
+        if self.prefetch:
+            self._pull_weight(0, buf ^ 1)                     # for the next call: runs under this call's second GEMM
+            self._w1_inflight = call + 1
         fc, dc = self.F // C, self.d_model // C
         for j in range(C):
-            for ev in self.ready[j]:
+            for ev in self.ready[buf][j]:
                 main.wait_event(ev)
             if record is not None:
                 record("start")
             b = self.b1[j * fc:(j + 1) * fc] if self.b1 is not None else None
-            capi.gemm_bf16(x, self.w1g[j], bias=b, epilogue=self.act, out=self.h[:, j * fc:(j + 1) * fc])
+            capi.gemm_bf16(x, self.w1g[buf, j], bias=b, epilogue=self.act, out=self.h[:, j * fc:(j + 1) * fc])
             if record is not None:
                 record("gemm1")
+        self.read[buf][0].record(main)
         for j in range(C):
-            for ev in self.ready[C + j]:
+            for ev in self.ready[buf][C + j]:
                 main.wait_event(ev)
             if record is not None:
                 record("start")
             b = self.b2[j * dc:(j + 1) * dc] if self.b2 is not None else None
-            capi.gemm_bf16(self.h, self.w2g[j], bias=b, epilogue=capi.EPI_BIAS if b is not None else capi.EPI_NONE,
+            capi.gemm_bf16(self.h, self.w2g[buf, j], bias=b, epilogue=capi.EPI_BIAS if b is not None else capi.EPI_NONE,
                            out=self.y[:, j * dc:(j + 1) * dc])
             if record is not None:
                 record("gemm2")
+        self.read[buf][1].record(main)
         return self.y
 
 
@@ -436,19 +495,26 @@ class FFNBench:
             # TFLOP/s), NCCL all-gather wins at 8 (4182 vs 3615); the one-kernel SM pull is behind both
             default_mode = "peer" if world <= 2 else "nccl"
             fsdp_mode = os.environ.get("B200_FSDP_COLLECTIVE", default_mode)
+            prefetch = os.environ.get("B200_FSDP_PREFETCH", "1") != "0"
+            # with the next call's W1 prefetched, each weight has a whole GEMM to arrive under: one chunk keeps the GEMMs at
+            # full waves (a d_model/4-column chunk of GEMM2 is 1.7 waves of tiles)
+            chunks = int(os.environ.get("B200_FSDP_CHUNKS", "1" if prefetch else str(chunks)))
             if fsdp_mode in ("peer", "peer_kernel"):
                 try:
-                    self.layer = PeerGatherFFN(*shard, act, tl, group, chunks=chunks,
+                    self.layer = PeerGatherFFN(*shard, act, tl, group, chunks=chunks, prefetch=prefetch,
                                                mode="kernel" if fsdp_mode == "peer_kernel" else "ce",
                                                copy_streams=1 if fsdp_mode == "peer_kernel" else 4)
                     self.collective = ("one-kernel SM pulls" if fsdp_mode == "peer_kernel" else "copy-engine pulls") + \
-                        " of weight column chunks from peer HBM over NVLink, overlapped with GEMMs"
+                        f" of weight column chunks ({chunks}) from peer HBM over NVLink, overlapped with GEMMs" + \
+                        (", W1 of the next call prefetched under GEMM2" if prefetch else "")
                 except Exception as e:   # noqa: BLE001
                     if rank == 0:
                         print(f"[bench] peer gather unavailable ({e!r}); using NCCL", file=sys.stderr, flush=True)
             if self.layer is None:
-                self.layer = FsdpFFN(*shard, act, tl, group, chunks=chunks)
-                self.collective = "NCCL all-gather of weight column chunks on a side stream"
+                self.layer = FsdpFFN(*shard, act, tl, group, chunks=chunks, prefetch=prefetch)
+                self.collective = f"NCCL all-gather of weight column chunks ({chunks}) on a side stream" + \
+                    (", W1 of the next call prefetched under GEMM2" if self.layer.prefetch else "") + \
+                    (f", GEMM grid {self.layer.gemm_max_ctas} CTAs" if self.layer.gemm_max_ctas else "")
             self.T_in, self.T_out = tl, tl
         else:
             fl = f // world
