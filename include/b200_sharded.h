@@ -54,6 +54,12 @@ typedef enum {
   B200_B_NK = 1  /* B is [N,K] row-major: C = A . B^T (e.g. Q.K^T, pre-transposed weights) */
 } b200_b_layout;
 
+/* Layout of the A operand (b200_gemm_args.a_layout). */
+typedef enum {
+  B200_A_MK = 0, /* A is [M,K] row-major */
+  B200_A_KM = 1  /* A is stored [K,M] row-major: C = A^T . B (weight gradients dW = x^T . dy) */
+} b200_a_layout;
+
 /* Library version (B200_VERSION of the build). */
 int b200_version(void);
 /* Message for the last non-OK status returned on this host thread ("" if none). */
@@ -115,6 +121,9 @@ typedef struct {
   void* const* c_block_ptrs;            /* device array of row-block base pointers, or NULL */
   int m_rows_per_block, m_block_rot;    /* 0 = off */
   int M, N, K, epilogue;
+  int a_layout;                         /* B200_A_MK (0): A is [M,K] row-major; B200_A_KM: A is stored [K,M] row-major,
+                                           i.e. the product is (stored A)^T . B -- the weight-gradient GEMM dW = x^T . dy of
+                                           jax.grad through nn.Dense (case5_attention_dense.py:130-139) */
 } b200_gemm_args;
 int b200_gemm_bf16_ex(const b200_gemm_args* args, void* stream);
 
@@ -147,6 +156,17 @@ int b200_attention_fwd(const void* Q, const void* K, const void* V, void* O, int
                        int64_t k_stride_s, int64_t k_stride_h, int64_t v_stride_b, int64_t v_stride_s,
                        int64_t v_stride_h, int64_t o_stride_b, int64_t o_stride_s, int64_t o_stride_h, float scale,
                        int causal, void* stream);
+
+/*
+ * optax.adam update of one f32 parameter tensor, in place (scale_by_adam, then scale(-lr), then apply_updates):
+ *   mu = b1 mu + (1-b1) g;  nu = b2 nu + (1-b2) g^2;
+ *   param -= lr * (mu / (1 - b1^step)) / (sqrt(nu / (1 - b2^step)) + eps)
+ * grad is f32 or bf16 (grad_dtype), step the 1-based update count after this call.  Replaces what
+ * TrainState.apply_gradients does with optax.adam(learning_rate=0.001) in the reference's train_step
+ *   (case5_attention_dense.py:107,130-139; case6_attention.py:181,206-220) -- SURVEY.md section 8(f) row 1.
+ */
+int b200_adam_step(float* param, const void* grad, int grad_dtype, float* mu, float* nu, int64_t n, float lr, float b1,
+                   float b2, float eps, int step, void* stream);
 
 /*
  * One device's share of the feed-forward block  y = act(x.W1 + b1).W2 (+ b2):

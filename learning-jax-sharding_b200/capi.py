@@ -22,6 +22,7 @@ LIB_PATH = os.path.join(_HERE, "libb200sl.so")
 BF16, F32 = 0, 1
 EPI_NONE, EPI_BIAS, EPI_BIAS_RELU, EPI_BIAS_GELU_TANH, EPI_RELU, EPI_GELU_TANH = range(6)
 B_KN, B_NK = 0, 1
+A_MK, A_KM = 0, 1
 
 EXPORTED_SYMBOLS = (
     "b200_version",
@@ -36,6 +37,7 @@ EXPORTED_SYMBOLS = (
     "b200_cast_f32_to_bf16",
     "b200_cast_bf16_to_f32",
     "b200_sum_partials_to_bf16",
+    "b200_adam_step",
     "b200_peer_alloc",
     "b200_peer_open",
     "b200_peer_close",
@@ -54,7 +56,7 @@ class GemmArgs(ctypes.Structure):
                 ("b_layout", ctypes.c_int), ("bias", ctypes.c_void_p), ("C", ctypes.c_void_p), ("ldc", ctypes.c_int64),
                 ("out_dtype", ctypes.c_int), ("c_block_ptrs", ctypes.c_void_p), ("m_rows_per_block", ctypes.c_int),
                 ("m_block_rot", ctypes.c_int), ("M", ctypes.c_int), ("N", ctypes.c_int), ("K", ctypes.c_int),
-                ("epilogue", ctypes.c_int)]
+                ("epilogue", ctypes.c_int), ("a_layout", ctypes.c_int)]
 
 
 class B200Error(RuntimeError):
@@ -99,7 +101,11 @@ def load():
     lib.b200_gemm_set_tuning.argtypes = [i32, i32]
     lib.b200_attention_set_variant.argtypes = [i32]
     lib.b200_gemm_set_group_m.argtypes = [i32]
-    for name in EXPORTED_SYMBOLS[3:] + ("b200_gemm_set_tuning", "b200_attention_set_variant", "b200_gemm_set_group_m"):
+    lib.b200_gemm_set_k_serpentine.argtypes = [i32]
+    lib.b200_gemm_set_max_ctas.argtypes = [i32]
+    lib.b200_adam_step.argtypes = [vp, vp, i32, vp, vp, i64, f32, f32, f32, f32, i32, vp]
+    for name in EXPORTED_SYMBOLS[3:] + ("b200_gemm_set_tuning", "b200_attention_set_variant", "b200_gemm_set_group_m",
+                                        "b200_gemm_set_k_serpentine", "b200_gemm_set_max_ctas"):
         getattr(lib, name).restype = i32
     _lib = lib
     return lib
@@ -192,6 +198,53 @@ def gemm_bf16(a, b, *, b_layout=B_KN, bias=None, epilogue=EPI_NONE, out=None, ou
             F32 if out.dtype == torch.float32 else BF16, M, N, K, epilogue, _stream(a))
     _check(rc, "b200_gemm_bf16")
     return out
+
+
+def gemm_bf16_tn(a_km, b, *, out=None, out_dtype=torch.bfloat16):
+    """out[M,N] = a_km^T @ b with a_km stored [K,M] and b [K,N], both row-major bf16: the weight-gradient product
+    dW = x^T @ dy of a Dense layer (b200_gemm_bf16_ex with a_layout = B200_A_KM; no transposed copy is made, the TMA
+    loads MN-major tiles)."""
+    _require_cuda(a_km, b, out)
+    if a_km.dtype != torch.bfloat16 or b.dtype != torch.bfloat16:
+        raise B200Error("gemm_bf16_tn takes bf16 operands")
+    if a_km.dim() != 2 or b.dim() != 2 or a_km.stride(1) != 1 or b.stride(1) != 1 or a_km.shape[0] != b.shape[0]:
+        raise B200Error(f"gemm_bf16_tn: need [K,M] and [K,N] operands, got {tuple(a_km.shape)} and {tuple(b.shape)}")
+    K, M = a_km.shape
+    N = b.shape[1]
+    if out is None:
+        out = torch.empty((M, N), dtype=out_dtype, device=b.device)
+    if out.shape != (M, N) or out.stride(1) != 1 or out.dtype not in (torch.bfloat16, torch.float32):
+        raise B200Error("gemm_bf16_tn: bad output tensor")
+    args = GemmArgs()
+    args.A, args.lda, args.a_layout = a_km.data_ptr(), a_km.stride(0), A_KM
+    args.B, args.ldb, args.b_layout = b.data_ptr(), b.stride(0), B_KN
+    args.C, args.ldc = out.data_ptr(), out.stride(0)
+    args.out_dtype = F32 if out.dtype == torch.float32 else BF16
+    args.M, args.N, args.K, args.epilogue = M, N, K, EPI_NONE
+    with torch.cuda.device(b.device):
+        rc = load().b200_gemm_bf16_ex(ctypes.byref(args), _stream(b))
+    _check(rc, "b200_gemm_bf16_ex")
+    return out
+
+
+def adam_step(param, grad, mu, nu, *, step: int, lr=1e-3, b1=0.9, b2=0.999, eps=1e-8):
+    """In-place optax.adam update of one f32 parameter tensor (b200_adam_step): mu, nu are the first / second moment
+    buffers, `step` the 1-based count AFTER this update; grad is f32 or bf16."""
+    _require_cuda(param, grad, mu, nu)
+    if param.dtype != torch.float32 or mu.dtype != torch.float32 or nu.dtype != torch.float32:
+        raise B200Error("adam_step: param, mu, nu must be fp32")
+    if grad.dtype not in (torch.float32, torch.bfloat16):
+        raise B200Error("adam_step: grad must be fp32 or bf16")
+    n = param.numel()
+    if not (param.is_contiguous() and grad.is_contiguous() and mu.is_contiguous() and nu.is_contiguous()) or \
+            grad.numel() != n or mu.numel() != n or nu.numel() != n:
+        raise B200Error("adam_step: tensors must be contiguous and of equal size")
+    with torch.cuda.device(param.device):
+        rc = load().b200_adam_step(_ptr(param), _ptr(grad), F32 if grad.dtype == torch.float32 else BF16, _ptr(mu), _ptr(nu),
+                                   ctypes.c_int64(n), ctypes.c_float(lr), ctypes.c_float(b1), ctypes.c_float(b2),
+                                   ctypes.c_float(eps), ctypes.c_int(step), _stream(param))
+    _check(rc, "b200_adam_step")
+    return param
 
 
 def gemm_f32(a, b, *, out=None, accumulate=False):

@@ -56,6 +56,8 @@ struct GemmParams {
   void* const* c_block_ptrs;
   int m_rows_per_block, m_block_rot, m_num_blocks;
   int num_stages;   // smem ring depth actually used (<= Cfg::kStages); tuning experiments only
+  int a_mn_major;   // 1: A is stored [K, M] row-major (the transposed operand of a weight-gradient GEMM dW = X^T . dY):
+                    // the A tile is loaded as two 64-row-wide MN-major chunks and the MMA reads it with the MN-major flag
   int k_serpentine; // 1: every other tile of a CTA walks K downwards, so a wave starts on the K range the previous wave
                     // has just left in L2 (the panels of one wave exceed L2 when K is large)
 };
@@ -166,7 +168,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (elect_one()) {
         if (G == 1) {
           mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
-          tma_load_2d(sa, &tmA, &full_bar[stage], k0, m0);
+          if (p.a_mn_major) {
+#pragma unroll
+            for (int c = 0; c < kBM / 64; ++c) tma_load_2d(sa + c * (kBK * 128), &tmA, &full_bar[stage], m0 + c * 64, k0);
+          } else {
+            tma_load_2d(sa, &tmA, &full_bar[stage], k0, m0);
+          }
           if (kBKmajor) {
             tma_load_2d(sb, &tmB, &full_bar[stage], k0, n0);
           } else {
@@ -177,7 +184,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         } else {
           // both CTAs' bytes complete on the leader's barrier
           if (leader) mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes * 2);
-          tma_load_2d_cg2(sa, &tmA, &full_bar[stage], k0, m0);
+          if (p.a_mn_major) {
+#pragma unroll
+            for (int c = 0; c < kBM / 64; ++c)
+              tma_load_2d_cg2(sa + c * (kBK * 128), &tmA, &full_bar[stage], m0 + c * 64, k0);
+          } else {
+            tma_load_2d_cg2(sa, &tmA, &full_bar[stage], k0, m0);
+          }
           if (kBKmajor) {
             tma_load_2d_cg2(sb, &tmB, &full_bar[stage], k0, n0);
           } else {
@@ -194,15 +207,18 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
   } else if (warp == 1 && leader) {
     // ===================== MMA issuer (leader CTA only) =====================
-    constexpr uint32_t idesc = make_idesc_bf16(kBM * G, BN, false, !kBKmajor);
+    const uint32_t idesc = p.a_mn_major ? make_idesc_bf16(kBM * G, BN, true, !kBKmajor)
+                                        : make_idesc_bf16(kBM * G, BN, false, !kBKmajor);
     // Descriptors of stage 0, built once; per MMA only a constant is added (the issuing thread has 128 cycles
     // per MMA at most -- rebuilding two 64-bit descriptors each time cost ~20 % of the tensor pipe).
     //   A: K-major, 32 bytes of K per MMA inside the 128-byte swizzle row.
     //   B K-major: same.  B MN-major ([K,N] row-major): 16 K-rows of 128 B per MMA, 64-column chunks kBK*128 B apart.
-    const uint64_t a_desc0 = make_smem_desc_sw128(smem_u32(smem), 16, 1024);
+    //   A MN-major ([K,M] row-major): like B MN-major, 64-row chunks kBK*128 B apart.
+    const uint64_t a_desc0 = p.a_mn_major ? make_smem_desc_sw128(smem_u32(smem), kBK * 128, 1024)
+                                          : make_smem_desc_sw128(smem_u32(smem), 16, 1024);
     const uint64_t b_desc0 = kBKmajor ? make_smem_desc_sw128(smem_u32(smem) + Cfg::kABytes, 16, 1024)
                                       : make_smem_desc_sw128(smem_u32(smem) + Cfg::kABytes, kBK * 128, 1024);
-    constexpr uint32_t kAStep = kUmmaK * 2;
+    const uint32_t kAStep = p.a_mn_major ? kUmmaK * 128 : kUmmaK * 2;
     constexpr uint32_t kBStep = kBKmajor ? kUmmaK * 2 : kUmmaK * 128;
     int stage = 0;
     uint32_t phase = 0;
@@ -419,6 +435,12 @@ static int launch_gemm(const void* A, int64_t lda, const void* B, int64_t ldb, c
     uint64_t dims[2] = {static_cast<uint64_t>(p.K), a_rows};
     uint64_t strides[2] = {0, static_cast<uint64_t>(lda) * 2};
     uint32_t box[2] = {kBK, kBM};
+    if (p.a_mn_major) {          // stored [K, M]: M is the contiguous dimension
+      dims[0] = static_cast<uint64_t>(p.M);
+      dims[1] = static_cast<uint64_t>(p.K);
+      box[0] = 64;
+      box[1] = kBK;
+    }
     int rc = make_tensor_map(&tmA, A, 2, 2, dims, strides, box, 3);
     if (rc != B200_OK) return rc;
   }
@@ -557,7 +579,11 @@ extern "C" int b200_gemm_bf16_ex(const b200_gemm_args* args, void* stream) {
       epilogue == B200_EPI_BIAS || epilogue == B200_EPI_BIAS_RELU || epilogue == B200_EPI_BIAS_GELU_TANH;
   B200_REQUIRE(!needs_bias || bias, "b200_gemm_bf16: epilogue %d needs a bias vector", epilogue);
   const int64_t min_ldb = b_layout == B200_B_KN ? N : K;
-  B200_REQUIRE(lda >= K && ldb >= min_ldb && ldc >= N, "b200_gemm_bf16: leading dimension smaller than row");
+  const bool a_km = args->a_layout == B200_A_KM;
+  B200_REQUIRE(args->a_layout == B200_A_MK || a_km, "b200_gemm_bf16: bad a_layout %d", args->a_layout);
+  B200_REQUIRE(!a_km || (a_rows_per_block == 0 && args->m_rows_per_block == 0 && M % 8 == 0),
+               "b200_gemm_bf16: a_layout KM needs M %% 8 == 0 and excludes the row-blocked / row-block-scatter options");
+  B200_REQUIRE(lda >= (a_km ? M : K) && ldb >= min_ldb && ldc >= N, "b200_gemm_bf16: leading dimension smaller than row");
   B200_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && ldc % 8 == 0, "b200_gemm_bf16: lda/ldb/ldc must be multiples of 8");
   B200_REQUIRE((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B) | reinterpret_cast<uintptr_t>(C) |
                 reinterpret_cast<uintptr_t>(bias)) % 16 == 0,
@@ -578,6 +604,7 @@ extern "C" int b200_gemm_bf16_ex(const b200_gemm_args* args, void* stream) {
   p.m_rows_per_block = args->m_rows_per_block;
   p.m_block_rot = args->m_block_rot;
   p.m_num_blocks = args->m_rows_per_block > 0 ? M / args->m_rows_per_block : 0;
+  p.a_mn_major = a_km ? 1 : 0;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const bool kmajor = b_layout == B200_B_NK;
 

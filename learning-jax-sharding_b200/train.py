@@ -1,0 +1,111 @@
+"""The training half of the reference's Dense module (first slice): what
+``train_step`` does in case5_attention_dense.py:130-139 -- ``loss = attention.apply(params, x).sum()``, ``jax.grad``,
+``state.apply_gradients`` with ``optax.adam(learning_rate=0.001)`` (:107) -- for a module that is one bf16
+``nn.Dense(use_bias=False)`` (:59-67), on the sharded state the script derives from its logical rules (:109-115).
+
+Host mirror of the pieces the script names: ``adam`` (optax.adam), ``TrainState.create / apply_gradients``
+(flax.training.train_state), and ``dense_sum_loss_grad`` (the kernel gradient jax.grad produces for that loss).  The
+arithmetic runs in the library: the weight-gradient product x^T . dy is b200_gemm_bf16_ex with a_layout = B200_A_KM
+(tcgen05, MN-major A tiles through TMA, no transposed copy), the update is b200_adam_step.  The backward of the attention
+module (case6_attention.py:206-220) is not built yet.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Callable, Dict, Optional
+
+import torch
+
+from . import runtime as _rt
+from .array import ShardedArray, reshard
+from .nn import _axes, _spec, _to_bf16
+from .sharding import NamedSharding
+
+
+@dataclass(frozen=True)
+class Adam:
+    """optax.adam(learning_rate, b1=0.9, b2=0.999, eps=1e-8): scale_by_adam, then scale(-learning_rate)."""
+    learning_rate: float = 1e-3
+    b1: float = 0.9
+    b2: float = 0.999
+    eps: float = 1e-8
+
+
+def adam(learning_rate: float = 1e-3, b1: float = 0.9, b2: float = 0.999, eps: float = 1e-8) -> Adam:
+    return Adam(learning_rate, b1, b2, eps)
+
+
+def _zeros_like(p: ShardedArray) -> ShardedArray:
+    return ShardedArray(p.shape, torch.float32, p.sharding, {d: torch.zeros_like(t, dtype=torch.float32)
+                                                             for d, t in p.local_shards.items()})
+
+
+class TrainState:
+    """flax.training.train_state.TrainState for f32 parameters held as ShardedArrays: ``step``, ``params``
+    (name -> ShardedArray), ``tx`` and the optimizer state (first / second moments in the parameters' sharding, which is
+    what ``nn.get_partition_spec`` + ``logical_to_mesh_sharding`` give the reference's state, case5_attention_dense.py
+    :113-115)."""
+
+    def __init__(self, step: int, apply_fn: Optional[Callable], params: Dict[str, ShardedArray], tx: Adam,
+                 mu: Dict[str, ShardedArray], nu: Dict[str, ShardedArray]):
+        self.step, self.apply_fn, self.params, self.tx, self.mu, self.nu = step, apply_fn, params, tx, mu, nu
+
+    @classmethod
+    def create(cls, *, apply_fn: Optional[Callable], params: Dict[str, ShardedArray], tx: Adam) -> "TrainState":
+        for name, p in params.items():
+            if p.dtype != torch.float32:
+                raise TypeError(f"TrainState keeps f32 parameters (flax's param_dtype); {name} is {p.dtype}")
+        return cls(0, apply_fn, dict(params), tx, {k: _zeros_like(p) for k, p in params.items()},
+                   {k: _zeros_like(p) for k, p in params.items()})
+
+    def apply_gradients(self, *, grads: Dict[str, ShardedArray]) -> "TrainState":
+        """One optimizer update, in place on every local shard (b200_adam_step); returns the state with step + 1."""
+        comp = _rt.local_compute()
+        rt = _rt.get_runtime()
+        step = self.step + 1
+        for name, p in self.params.items():
+            g = grads[name]
+            if not g.sharding.same_layout(p.sharding, p.shape):
+                g = reshard(g, p.sharding)
+            for d in rt.local_device_ids:
+                if d in p.local_shards:
+                    comp.adam_step(p.shard(d), g.shard(d).contiguous(), self.mu[name].shard(d), self.nu[name].shard(d),
+                                   step=step, lr=self.tx.learning_rate, b1=self.tx.b1, b2=self.tx.b2, eps=self.tx.eps)
+        return TrainState(step, self.apply_fn, self.params, self.tx, self.mu, self.nu)
+
+
+def dense_sum_loss_grad(x: ShardedArray, kernel: ShardedArray) -> ShardedArray:
+    """d/d kernel of ``nn.dense(x, kernel).sum()`` in the kernel's sharding, f32 holding bf16-valued numbers (the oracle's
+    ``dense_sum_loss_grads``): on every device the partial product x_local^T . ones[rows_local, N_local] with f32
+    accumulation and f32 output, an all-reduce over the mesh axes that shard the rows of x (the data-parallel gradient
+    reduction), ONE rounding to bf16 as the unsharded dot would apply, then local slicing to the kernel's sharding."""
+    rt = _rt.get_runtime()
+    comp = _rt.local_compute()
+    mesh = x.sharding.mesh
+    xa = _axes(x)
+    rows, kx = xa[:-1], xa[-1]
+    row_axes = tuple(a for r in rows for a in r)
+    kw, nw = _axes(kernel)
+    # the forward (nn.dense) cannot shard y's features over an axis the rows of x use: the cotangent follows y
+    nw_eff = tuple(a for a in nw if a not in row_axes)
+    kdim, ndim = kernel.shape
+    part = {}
+    for d in rt.local_device_ids:
+        xs = x.shard(d)
+        x2 = _to_bf16(xs.reshape(-1, xs.shape[-1]))
+        n_local = ndim
+        for a in nw_eff:
+            n_local //= mesh.shape[a]
+        dy = torch.ones((x2.shape[0], n_local), dtype=torch.bfloat16, device=x2.device)
+        part[d] = comp.gemm_bf16_tn(x2, dy, out_dtype=torch.float32)
+    if row_axes:
+        part = rt.all_reduce(part, mesh.axis_groups(row_axes))
+    # one rounding to bf16, kept as f32 (promote_dtype's cast of the cotangent back to the f32 param dtype)
+    part = {d: comp.cast_bf16_to_f32(comp.cast_f32_to_bf16(t.contiguous())) for d, t in part.items()}
+    grad = ShardedArray((kdim, ndim), torch.float32, NamedSharding(mesh, _spec([kx, nw_eff])), part)
+    return reshard(grad, kernel.sharding)
+
+
+def dense_train_step(state: TrainState, x: ShardedArray, name: str = "kernel") -> TrainState:
+    """train_step of case5_attention_dense.py:130-139 for the single-Dense module: grads of sum(Dense(x)), then Adam."""
+    return state.apply_gradients(grads={name: dense_sum_loss_grad(x, state.params[name])})

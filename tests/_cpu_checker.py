@@ -59,3 +59,20 @@ def sum_partials_to_bf16(partials, bias=None, out=None):
     if bias is not None:
         v = _r(v + bias.to(F32))
     return v.to(BF16)
+
+
+def gemm_bf16_tn(a_km, b, *, out=None, out_dtype=BF16):
+    acc = a_km.to(F32).t() @ b.to(F32)
+    res = acc if out_dtype == F32 else _r(acc).to(out_dtype)
+    if out is not None:
+        out.copy_(res)
+        return out
+    return res
+
+
+def adam_step(param, grad, mu, nu, *, step, lr=1e-3, b1=0.9, b2=0.999, eps=1e-8):
+    p2, mu2, nu2 = rm.adam_update(param, grad, mu, nu, step, lr=lr, b1=b1, b2=b2, eps=eps)
+    param.copy_(p2)
+    mu.copy_(mu2)
+    nu.copy_(nu2)
+    return param

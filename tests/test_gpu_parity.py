@@ -392,3 +392,66 @@ def test_host_buffer_ffn_step_matches_oracle(ljs):
     assert outs[0].data_ptr() != outs[1].data_ptr() and outs[0].data_ptr() == outs[2].data_ptr()
     for o in outs[-2:]:
         assert torch.equal(o, first)
+
+
+# ------------------------------------------------------------------------------ train_step of the Dense module (8f row 1)
+@pytest.mark.parametrize("shape", [(64, 128, 128), (2048, 640, 512), (1000, 264, 72), (8192, 1024, 2048), (4096, 4096, 512)])
+def test_weight_gradient_gemm_tn(ljs, shape):
+    """dW = x^T . dy with x stored [T, K_in] (b200_gemm_bf16_ex, a_layout = B200_A_KM) against f32-accumulate math."""
+    T, M, N = shape
+    x = rm.synthetic((T, M), 70).to(torch.bfloat16)
+    dy = rm.synthetic((T, N), 71).to(torch.bfloat16)
+    want = x.float().t() @ dy.float()
+    got32 = ljs.capi.gemm_bf16_tn(_dev(x), _dev(dy), out_dtype=torch.float32).cpu()
+    torch.testing.assert_close(got32, want, rtol=1e-4, atol=1e-3 * T ** 0.5)
+    got16 = ljs.capi.gemm_bf16_tn(_dev(x), _dev(dy)).cpu()
+    torch.testing.assert_close(got16.float(), want.to(torch.bfloat16).float(), **BF16_TOL)
+
+
+def test_weight_gradient_gemm_tn_rejects_bad_arguments(ljs):
+    x = _dev(rm.synthetic((64, 100), 72).to(torch.bfloat16))          # M = 100 is not a multiple of 8
+    dy = _dev(rm.synthetic((64, 64), 73).to(torch.bfloat16))
+    with pytest.raises(ljs.capi.B200Error):
+        ljs.capi.gemm_bf16_tn(x, dy)
+    with pytest.raises(ljs.capi.B200Error):
+        ljs.capi.gemm_bf16_tn(_dev(rm.synthetic((32, 64), 74).to(torch.bfloat16)), dy)   # contraction mismatch
+
+
+@pytest.mark.parametrize("n", [8, 1000, 640 * 512, 1 << 22])
+@pytest.mark.parametrize("grad_dtype", [torch.float32, torch.bfloat16])
+def test_adam_step_matches_oracle(ljs, n, grad_dtype):
+    p = rm.synthetic((n,), 80)
+    g = rm.synthetic((n,), 81).to(grad_dtype)
+    mu, nu = torch.zeros(n), torch.zeros(n)
+    dp, dmu, dnu = _dev(p.clone()), _dev(mu.clone()), _dev(nu.clone())
+    for step in (1, 2, 3):
+        p, mu, nu = rm.adam_update(p, g, mu, nu, step)
+        ljs.capi.adam_step(dp, _dev(g), dmu, dnu, step=step)
+        torch.testing.assert_close(dp.cpu(), p, rtol=0, atol=3e-7)       # |p| ~ 1: a few f32 ulps of the update
+        torch.testing.assert_close(dmu.cpu(), mu, rtol=2e-6, atol=1e-9)
+        torch.testing.assert_close(dnu.cpu(), nu, rtol=2e-6, atol=1e-12)
+
+
+@pytest.mark.parametrize("wspec", [("embed", "kv"), ("embed", "hidden")])
+def test_dense_train_step_literal_case5(ljs, wspec):
+    """case5_attention_dense.py at its literal size (x (8,256,640), kernel (640,512), 2x2 mesh, the script's rules):
+    two train steps on four virtual devices against the unsharded oracle."""
+    ljs.init_virtual(4, "cuda:0")
+    mesh = ljs.Mesh(ljs.create_device_mesh((2, 2)), ("data", "model"))
+    P = ljs.PartitionSpec
+    rules = (("batch", "data"), ("embed", "data"), ("hidden", "model"))
+    x_host, w_host = rm.synthetic((8, 256, 640), 1), rm.synthetic((640, 512), 2, "weight")
+    x = ljs.device_put(x_host, ljs.NamedSharding(mesh, P("data", "model")))
+    w = ljs.device_put(w_host.clone(), ljs.nn.logical_to_mesh_sharding(wspec, mesh, rules))
+    state = ljs.train.TrainState.create(apply_fn=None, params={"kernel": w}, tx=ljs.train.adam(learning_rate=0.001))
+    g = ljs.train.dense_sum_loss_grad(x, w)
+    g_want, _ = rm.dense_sum_loss_grads(x_host, w_host)
+    torch.testing.assert_close(g.global_array().cpu(), g_want, rtol=2 ** -7, atol=0)
+    k, mu, nu = w_host.clone(), torch.zeros_like(w_host), torch.zeros_like(w_host)
+    for step in (1, 2):
+        state = ljs.train.dense_train_step(state, x)
+        k, mu, nu, _ = rm.dense_train_step(x_host, k, mu, nu, step)
+        torch.testing.assert_close(state.params["kernel"].global_array().cpu(), k, rtol=0, atol=2e-5)
+    # forward with the updated parameters still matches the oracle's forward
+    y = ljs.nn.dense(x, state.params["kernel"])
+    torch.testing.assert_close(y.global_array().cpu().float(), rm.dense_bf16(x_host, k).float(), **BF16_TOL)

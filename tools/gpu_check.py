@@ -350,6 +350,30 @@ def main():
             print(f"  {name:5s} {ms:.3f} ms {fl / ms / 1e9:7.1f} TFLOP/s  sm {mhz} MHz (min {c.get('sm_min_mhz')}) "
                   f"power max {c.get('power_w_max')} W {c.get('reasons')}  -> {cyc:.0f} cycles per CTA-tile", flush=True)
         capi.set_attention_variant(0)
+    elif args.what == "train_time":
+        # the two kernels of the Dense train_step at the case5 config size: weight-gradient GEMM (x^T . dy) and Adam
+        T, M, N = 32768, 4096, 4096
+        x = torch.randn(T, M, device="cuda").to(torch.bfloat16)
+        dy = torch.randn(T, N, device="cuda").to(torch.bfloat16)
+        out = torch.empty(M, N, device="cuda", dtype=torch.float32)
+        ms = time_fn(lambda: capi.gemm_bf16_tn(x, dy, out=out), iters=10, warmup=3)
+        print(f"  dW = x^T . dy  T={T} M={M} N={N}: {ms:.3f} ms {2.0 * T * M * N / ms / 1e9:.1f} TFLOP/s", flush=True)
+        xt = x.t().contiguous()
+        ms2 = time_fn(lambda: capi.gemm_bf16(xt, dy, out=out), iters=10, warmup=3)
+        print(f"  same product from a pre-transposed x (K-major A): {ms2:.3f} ms {2.0 * T * M * N / ms2 / 1e9:.1f} TFLOP/s", flush=True)
+        want = torch.matmul(x.float().t()[:256], dy.float())
+        err = (out[:256] - want).abs().max().item()
+        print(f"  max |err| on 256 rows vs fp32 matmul: {err:.3e}", flush=True)
+        ok &= err < 0.5
+        n = M * N
+        p, mu, nu = (torch.randn(n, device="cuda") for _ in range(3))
+        nu.abs_()
+        g = torch.randn(n, device="cuda")
+        ms3 = time_fn(lambda: capi.adam_step(p, g, mu, nu, step=3), iters=20, warmup=3)
+        print(f"  adam_step n={n} (f32 grad): {ms3:.4f} ms {28.0 * n / ms3 / 1e6:.0f} GB/s (28 B per element)", flush=True)
+        gb = g.to(torch.bfloat16)
+        ms4 = time_fn(lambda: capi.adam_step(p, gb, mu, nu, step=3), iters=20, warmup=3)
+        print(f"  adam_step n={n} (bf16 grad): {ms4:.4f} ms {26.0 * n / ms4 / 1e6:.0f} GB/s (26 B per element)", flush=True)
     elif args.what == "attn_quick":
         # one line per call, for A/B runs of library variants: burst (5 iterations) non-causal / causal and a sustained
         # run (300 launches) with the NVML clock, all at B8 S4096 H32 D128
