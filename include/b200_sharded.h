@@ -253,6 +253,35 @@ int b200_peer_barrier(void* const* flag_ptrs_dev, int rank, int world, uint32_t 
 int b200_sum_bf16_partials(const void* src, int64_t src_stride, int nsrc, const void* bias, int64_t cols, void* dst,
                            int64_t n, void* stream);
 
+/*
+ * Mesh-axis communicators and collectives for a binder that runs one process per GPU.
+ * Replaces, at the device level, Mesh(create_device_mesh((2,4)), ('data','model')) (case1a.py:15;
+ * case6_attention.py:155-156) and the psum / all_gather / psum_scatter / all_to_all XLA inserts around sharded
+ * dots and at with_logical_constraint boundaries (case1a.py:49; case6_attention.py:137,141,229-237).
+ * Transport is NCCL (libnccl.so.2 resolved with dlopen at first use; B200_ERR_UNSUPPORTED if absent).
+ *   b200_comm_unique_id  rank 0 fills a 128-byte id and hands it to the other ranks by any host-side channel.
+ *   b200_mesh_create     SET-UP, collective over all ranks: rank r sits at the row-major coordinates of r in
+ *                        `shape` (last axis fastest: device id = 4x + y on a 2x4 mesh, as create_device_mesh).
+ *   b200_mesh_axis_comm  communicator of the ranks that differ from this one only along `axis`, ordered by that
+ *                        coordinate; the first call per axis is collective over the mesh (ncclCommSplit).
+ *   b200_all_reduce / reduce_scatter / all_gather / all_to_all   enqueue-only on `stream`, sum reduction,
+ *                        dtype B200_BF16 or B200_F32, counts in elements (see csrc/mesh_comm.cu for block layouts).
+ * The hot FFN / attention layers do not use these: their reduce-scatter is fused into the GEMM epilogue (b200_peer_*).
+ */
+typedef struct b200_mesh b200_mesh;
+typedef struct b200_comm b200_comm;
+int b200_comm_unique_id(void* out128);
+int b200_mesh_create(const void* unique_id128, int world, int rank, const int* shape, int naxes, b200_mesh** out);
+int b200_mesh_axis_comm(b200_mesh* mesh, int axis, b200_comm** out);
+int b200_comm_size(const b200_comm* comm);
+int b200_comm_rank(const b200_comm* comm);
+int b200_comm_release(b200_comm* comm);
+int b200_mesh_destroy(b200_mesh* mesh);
+int b200_all_reduce(b200_comm* comm, const void* send, void* recv, int64_t count, int dtype, void* stream);
+int b200_reduce_scatter(b200_comm* comm, const void* send, void* recv, int64_t recv_count, int dtype, void* stream);
+int b200_all_gather(b200_comm* comm, const void* send, void* recv, int64_t send_count, int dtype, void* stream);
+int b200_all_to_all(b200_comm* comm, const void* send, void* recv, int64_t count, int dtype, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

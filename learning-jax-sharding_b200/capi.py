@@ -38,6 +38,17 @@ EXPORTED_SYMBOLS = (
     "b200_cast_bf16_to_f32",
     "b200_sum_partials_to_bf16",
     "b200_adam_step",
+    "b200_comm_unique_id",
+    "b200_mesh_create",
+    "b200_mesh_axis_comm",
+    "b200_comm_size",
+    "b200_comm_rank",
+    "b200_comm_release",
+    "b200_mesh_destroy",
+    "b200_all_reduce",
+    "b200_reduce_scatter",
+    "b200_all_gather",
+    "b200_all_to_all",
     "b200_peer_alloc",
     "b200_peer_open",
     "b200_peer_close",
@@ -104,6 +115,15 @@ def load():
     lib.b200_gemm_set_k_serpentine.argtypes = [i32]
     lib.b200_gemm_set_max_ctas.argtypes = [i32]
     lib.b200_adam_step.argtypes = [vp, vp, i32, vp, vp, i64, f32, f32, f32, f32, i32, vp]
+    lib.b200_comm_unique_id.argtypes = [vp]
+    lib.b200_mesh_create.argtypes = [vp, i32, i32, ctypes.POINTER(i32), i32, ctypes.POINTER(vp)]
+    lib.b200_mesh_axis_comm.argtypes = [vp, i32, ctypes.POINTER(vp)]
+    lib.b200_comm_size.argtypes = [vp]
+    lib.b200_comm_rank.argtypes = [vp]
+    lib.b200_comm_release.argtypes = [vp]
+    lib.b200_mesh_destroy.argtypes = [vp]
+    for _n in ("b200_all_reduce", "b200_reduce_scatter", "b200_all_gather", "b200_all_to_all"):
+        getattr(lib, _n).argtypes = [vp, vp, vp, i64, i32, vp]
     for name in EXPORTED_SYMBOLS[3:] + ("b200_gemm_set_tuning", "b200_attention_set_variant", "b200_gemm_set_group_m",
                                         "b200_gemm_set_k_serpentine", "b200_gemm_set_max_ctas"):
         getattr(lib, name).restype = i32
@@ -374,6 +394,87 @@ def gemm_bf16_scatter(a, b, block_ptrs, rows_per_block: int, rot: int, ldc: int,
     with torch.cuda.device(a.device):
         rc = load().b200_gemm_bf16_ex(ctypes.byref(args), _stream(a))
     _check(rc, "b200_gemm_bf16_ex")
+
+
+def comm_unique_id() -> bytes:
+    """128-byte id for mesh_create (rank 0 makes it, every rank passes the same bytes)."""
+    buf = ctypes.create_string_buffer(128)
+    _check(load().b200_comm_unique_id(buf), "b200_comm_unique_id")
+    return buf.raw
+
+
+class MeshComm:
+    """b200_mesh_* / b200_all_reduce ... of include/b200_sharded.h on torch tensors: a device mesh with one NCCL
+    communicator per mesh axis, for one process per GPU.  Collective at construction and at the first use of an axis."""
+
+    def __init__(self, unique_id: bytes, world: int, rank: int, shape):
+        self.shape = tuple(int(v) for v in shape)
+        arr = (ctypes.c_int * len(self.shape))(*self.shape)
+        self._mesh = ctypes.c_void_p()
+        _check(load().b200_mesh_create(ctypes.create_string_buffer(unique_id, 128), world, rank, arr, len(self.shape),
+                                       ctypes.byref(self._mesh)), "b200_mesh_create")
+        self._comms = {}
+
+    def _comm(self, axis: int):
+        if axis not in self._comms:
+            c = ctypes.c_void_p()
+            _check(load().b200_mesh_axis_comm(self._mesh, axis, ctypes.byref(c)), "b200_mesh_axis_comm")
+            self._comms[axis] = c
+        return self._comms[axis]
+
+    def axis_size(self, axis: int) -> int:
+        return load().b200_comm_size(self._comm(axis))
+
+    def axis_rank(self, axis: int) -> int:
+        return load().b200_comm_rank(self._comm(axis))
+
+    @staticmethod
+    def _dt(t):
+        if t.dtype == torch.bfloat16:
+            return BF16
+        if t.dtype == torch.float32:
+            return F32
+        raise B200Error("mesh collectives take bf16 or fp32 tensors")
+
+    def all_reduce(self, t, axis: int):
+        """In-place sum of ``t`` over the mesh axis."""
+        _require_cuda(t)
+        _check(load().b200_all_reduce(self._comm(axis), _ptr(t), _ptr(t), t.numel(), self._dt(t), _stream(t)), "b200_all_reduce")
+        return t
+
+    def reduce_scatter(self, t, axis: int):
+        """``t`` = axis_size consecutive blocks along dim 0; returns the sum of everybody's block [axis_rank]."""
+        _require_cuda(t)
+        n = self.axis_size(axis)
+        out = torch.empty((t.shape[0] // n,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+        _check(load().b200_reduce_scatter(self._comm(axis), _ptr(t), _ptr(out), out.numel(), self._dt(t), _stream(t)),
+               "b200_reduce_scatter")
+        return out
+
+    def all_gather(self, t, axis: int):
+        """Concatenation of the ranks' ``t`` along dim 0, in axis order."""
+        _require_cuda(t)
+        n = self.axis_size(axis)
+        out = torch.empty((t.shape[0] * n,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+        _check(load().b200_all_gather(self._comm(axis), _ptr(t), _ptr(out), t.numel(), self._dt(t), _stream(t)), "b200_all_gather")
+        return out
+
+    def all_to_all(self, t, axis: int):
+        """Block p of ``t`` (dim 0 split in axis_size blocks) goes to rank p; returns the blocks received, in rank order."""
+        _require_cuda(t)
+        n = self.axis_size(axis)
+        out = torch.empty_like(t)
+        _check(load().b200_all_to_all(self._comm(axis), _ptr(t), _ptr(out), t.numel() // n, self._dt(t), _stream(t)),
+               "b200_all_to_all")
+        return out
+
+    def destroy(self):
+        for c in self._comms.values():
+            load().b200_comm_release(c)
+        self._comms = {}
+        if self._mesh:
+            _check(load().b200_mesh_destroy(self._mesh), "b200_mesh_destroy")
+            self._mesh = ctypes.c_void_p()
 
 
 def peer_alloc(nbytes: int):

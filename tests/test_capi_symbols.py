@@ -52,3 +52,18 @@ def test_missing_library_fails_loudly(ljs, monkeypatch, tmp_path):
     monkeypatch.setattr(ljs.capi, "LIB_PATH", str(tmp_path / "nope.so"))
     with pytest.raises(ljs.capi.B200Error, match="no CPU/PyTorch fallback"):
         ljs.capi.load()
+
+
+def test_mesh_create_rejects_bad_shapes_before_touching_nccl(ljs):
+    """Argument checks of b200_mesh_create run on the host before any NCCL call (no GPU needed)."""
+    import ctypes
+    capi = ljs.capi
+    lib = capi.load()
+    mesh = ctypes.c_void_p()
+    uid = ctypes.create_string_buffer(128)
+    for shape, world, rank in [((2, 4), 4, 0), ((2, 0), 0, 0), ((2, 2), 4, 7)]:
+        arr = (ctypes.c_int * len(shape))(*shape)
+        rc = lib.b200_mesh_create(uid, world, rank, arr, len(shape), ctypes.byref(mesh))
+        assert rc == 1, (shape, world, rank)                       # B200_ERR_INVALID_ARGUMENT
+        assert b"b200_mesh_create" in lib.b200_last_error()
+    assert lib.b200_comm_size(None) == -1 and lib.b200_mesh_destroy(None) == 0

@@ -108,6 +108,42 @@ def main():
     good = bool(((got - ref).abs() <= 2e-2 * ref.abs() + 2e-2).all())
     print(f"[rank {rank}] nn.ffn (NamedSharding, NCCL reduce-scatter): {'OK' if good else 'FAIL'}", flush=True)
     ok &= good
+    # the C-ABI mesh communicators (b200_mesh_* / b200_all_reduce ...): every collective on every axis of a (2, world/2)
+    # mesh (or a 1-D mesh) against values computed locally (every rank can reconstruct the others' inputs)
+    uid = [ljs.capi.comm_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(uid, src=0)
+    shape = (2, world // 2) if world % 2 == 0 and world > 2 else (world,)
+    mc = ljs.capi.MeshComm(uid[0], world, rank, shape)
+    def coords_of(q):                              # row-major: last axis fastest
+        c = []
+        for sz in reversed(shape):
+            c.insert(0, q % sz)
+            q //= sz
+        return c
+    coords = coords_of(rank)
+    good = True
+    for axis, n in enumerate(shape):
+        members = [q for q in range(world)
+                   if all(cq == cr for i, (cq, cr) in enumerate(zip(coords_of(q), coords)) if i != axis)]
+        good &= mc.axis_size(axis) == n and mc.axis_rank(axis) == coords[axis] and len(members) == n
+        for dt in (torch.float32, torch.bfloat16):
+            base = torch.arange(n * 8 * 16, device=dev, dtype=torch.float32).reshape(n * 8, 16) / 64.0
+            mine = (base + rank).to(dt)
+            theirs = [(base + q).to(dt) for q in members]
+            want_sum = torch.stack([t.float() for t in theirs]).sum(0)
+            got = mc.all_reduce(mine.clone(), axis)
+            good &= bool(torch.allclose(got.float(), want_sum, rtol=2e-2, atol=2e-2))
+            got = mc.reduce_scatter(mine.clone(), axis)
+            blk = slice(coords[axis] * 8, (coords[axis] + 1) * 8)
+            good &= bool(torch.allclose(got.float(), want_sum[blk], rtol=2e-2, atol=2e-2))
+            got = mc.all_gather(mine[:8].contiguous(), axis)
+            good &= bool(torch.equal(got, torch.cat([t[:8] for t in theirs])))
+            got = mc.all_to_all(mine.clone(), axis)
+            good &= bool(torch.equal(got, torch.cat([t[blk] for t in theirs])))
+    torch.cuda.synchronize()
+    mc.destroy()
+    print(f"[rank {rank}] C-ABI mesh collectives on mesh {shape}: {'OK' if good else 'FAIL'}", flush=True)
+    ok &= good
     # the streaming host-buffer step bench.py times as `e2e`, in both shardings: several overlapping calls, every returned
     # pinned buffer against the oracle rows this rank owns
     for mode in ("tp", "fsdp"):
