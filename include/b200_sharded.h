@@ -282,6 +282,22 @@ int b200_reduce_scatter(b200_comm* comm, const void* send, void* recv, int64_t r
 int b200_all_gather(b200_comm* comm, const void* send, void* recv, int64_t send_count, int dtype, void* stream);
 int b200_all_to_all(b200_comm* comm, const void* send, void* recv, int64_t count, int dtype, void* stream);
 
+/*
+ * The tensor-parallel FFN with its reduction: b200_ffn_fwd's two GEMMs on this device's W1 columns / W2 rows, then
+ * the sum over the mesh axis of `comm` -- reduce_mode B200_REDUCE_ALL: y [T, d_model] bf16 on every rank (psum);
+ * B200_REDUCE_SCATTER: y [T / size, d_model] = this rank's sequence block (psum_scatter, the out_shardings of
+ * case6_attention.py:229-232).  `chunks` token chunks: the collective of chunk c runs on an internal stream under
+ * GEMM2 of chunk c+1 (reduce-scatter in chunks needs T / (size * chunks) % 128 == 0).  h [T, F] bf16 and partial
+ * [T, d_model] f32 are caller-provided workspaces; b2 is added after the reduction (pass it on every rank).
+ * The first call on a device creates the internal stream and events (set-up: before any stream capture).
+ * Reference: the FFN comment case6_attention.py:36-40 with the all-reduce XLA inserts after a contraction-sharded dot
+ * (case1a.py:49).  This repo's throughput path is the fused peer-memory variant (b200_gemm_bf16_ex + b200_peer_*).
+ */
+typedef enum { B200_REDUCE_ALL = 0, B200_REDUCE_SCATTER = 1 } b200_reduce_mode;
+int b200_ffn_fwd_tp(b200_comm* comm, const void* x, const void* W1, const void* b1, const void* W2, const void* b2,
+                    void* h, float* partial, void* y, int reduce_mode, int T, int d_model, int F, int act, int chunks,
+                    void* stream);
+
 #ifdef __cplusplus
 }
 #endif

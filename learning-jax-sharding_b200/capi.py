@@ -49,6 +49,7 @@ EXPORTED_SYMBOLS = (
     "b200_reduce_scatter",
     "b200_all_gather",
     "b200_all_to_all",
+    "b200_ffn_fwd_tp",
     "b200_peer_alloc",
     "b200_peer_open",
     "b200_peer_close",
@@ -122,6 +123,7 @@ def load():
     lib.b200_comm_rank.argtypes = [vp]
     lib.b200_comm_release.argtypes = [vp]
     lib.b200_mesh_destroy.argtypes = [vp]
+    lib.b200_ffn_fwd_tp.argtypes = [vp] * 9 + [i32] * 6 + [vp]
     for _n in ("b200_all_reduce", "b200_reduce_scatter", "b200_all_gather", "b200_all_to_all"):
         getattr(lib, _n).argtypes = [vp, vp, vp, i64, i32, vp]
     for name in EXPORTED_SYMBOLS[3:] + ("b200_gemm_set_tuning", "b200_attention_set_variant", "b200_gemm_set_group_m",
@@ -467,6 +469,23 @@ class MeshComm:
         _check(load().b200_all_to_all(self._comm(axis), _ptr(t), _ptr(out), t.numel() // n, self._dt(t), _stream(t)),
                "b200_all_to_all")
         return out
+
+    def ffn_fwd_tp(self, axis: int, x, w1, b1, w2, b2, *, act=EPI_BIAS_GELU_TANH, reduce_scatter=False, chunks=1):
+        """b200_ffn_fwd_tp: this rank's W1 columns / W2 rows, the sum over the mesh axis inside the call.  Returns y
+        [T, d_model] (all-reduce) or [T / axis_size, d_model] (reduce-scatter: this rank's sequence block)."""
+        _require_cuda(x, w1, b1, w2, b2)
+        T, d_model = x.shape
+        F = w1.shape[1]
+        n = self.axis_size(axis)
+        h = torch.empty((T, F), dtype=torch.bfloat16, device=x.device)
+        partial = torch.empty((T, d_model), dtype=torch.float32, device=x.device)
+        y = torch.empty((T // n if reduce_scatter else T, d_model), dtype=torch.bfloat16, device=x.device)
+        with torch.cuda.device(x.device):
+            rc = load().b200_ffn_fwd_tp(self._comm(axis), _ptr(x), _ptr(w1), _ptr(b1), _ptr(w2), _ptr(b2), _ptr(h),
+                                        _ptr(partial), _ptr(y), 1 if reduce_scatter else 0, T, d_model, F, act, chunks,
+                                        _stream(x))
+        _check(rc, "b200_ffn_fwd_tp")
+        return y
 
     def destroy(self):
         for c in self._comms.values():

@@ -140,9 +140,26 @@ def main():
             good &= bool(torch.equal(got, torch.cat([t[:8] for t in theirs])))
             got = mc.all_to_all(mine.clone(), axis)
             good &= bool(torch.equal(got, torch.cat([t[blk] for t in theirs])))
+    # b200_ffn_fwd_tp: the tensor-parallel FFN with its reduction inside the C call, over the LAST mesh axis; ranks that
+    # differ along the other axis hold the same shard and must agree
+    ax = len(shape) - 1
+    n_ax, r_ax = shape[ax], coords[ax]
+    fl2 = f // n_ax
+    w1s, b1s = bf(w1[:, r_ax * fl2:(r_ax + 1) * fl2].contiguous()), bf(b1[r_ax * fl2:(r_ax + 1) * fl2])
+    w2s = bf(w2[r_ax * fl2:(r_ax + 1) * fl2].contiguous())
+    for rs in (False, True):
+        for ch in (1, 2):
+            y = mc.ffn_fwd_tp(ax, bf(x), w1s, b1s, w2s, bf(b2), reduce_scatter=rs, chunks=ch)
+            torch.cuda.synchronize()
+            blk2 = T // n_ax
+            ref = want[r_ax * blk2:(r_ax + 1) * blk2] if rs else want
+            g2 = bool(((y.cpu().float() - ref).abs() <= 2e-2 * ref.abs() + 2e-2).all())
+            if not g2:
+                print(f"[rank {rank}] b200_ffn_fwd_tp reduce_scatter={rs} chunks={ch}: FAIL", flush=True)
+            good &= g2
     torch.cuda.synchronize()
     mc.destroy()
-    print(f"[rank {rank}] C-ABI mesh collectives on mesh {shape}: {'OK' if good else 'FAIL'}", flush=True)
+    print(f"[rank {rank}] C-ABI mesh collectives + b200_ffn_fwd_tp on mesh {shape}: {'OK' if good else 'FAIL'}", flush=True)
     ok &= good
     # the streaming host-buffer step bench.py times as `e2e`, in both shardings: several overlapping calls, every returned
     # pinned buffer against the oracle rows this rank owns
