@@ -39,6 +39,9 @@ namespace b200 {
 #define B200_ATTN9_QK_FIRST 1   // MMA issue order when both are ready: Q.K^T (what the softmax waits for next) before P.V
 #endif
 
+#ifndef B200_ATTN9_OVERLAP
+#define B200_ATTN9_OVERLAP 0    // 1: second half of the S load under the max of the first, first half of the P store under
+#endif                          //    the exp of the second (A/B: profiles/r01_attention_v9_ab.log)
 #ifndef B200_ATTN9_POLY
 #define B200_ATTN9_POLY 0       // n > 0: every (1 << n)-th pair of exp2 goes to a degree-3 polynomial on the FMA pipe
 #endif
@@ -443,27 +446,54 @@ attention_fwd9_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
           uint32_t(&s3)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[96]);
           tmem_ld_32x32(s_tmem, s0);
           tmem_ld_32x32(s_tmem + 32, s1);
+#if B200_ATTN9_OVERLAP
+          tmem_wait_ld();
+#endif
           tmem_ld_32x32(s_tmem + 64, s2);
           tmem_ld_32x32(s_tmem + 96, s3);
+#if !B200_ATTN9_OVERLAP
           tmem_wait_ld();
+#endif
         }
+        float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        const bool any_mask = __any_sync(0xffffffffu, need_mask);
+#if B200_ATTN9_OVERLAP
+        if (!any_mask) {                         // max of keys [0, 64) while keys [64, 128) are still arriving
+#pragma unroll
+          for (int i = 0; i < 64; i += 8) {
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+              mx4[c] = max3n(mx4[c], __uint_as_float(s[i + 2 * c]), __uint_as_float(s[i + 2 * c + 1]));
+          }
+        }
+        tmem_wait_ld();
+#endif
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_remote(&s_free[b], 0);   // S[b] may be overwritten by Q.K^T of tile T+2
         PROF_MARK9(1);
-        if (__any_sync(0xffffffffu, need_mask)) {
+        if (any_mask) {
           asm volatile("" ::: "memory");         // keep this a branch: only diagonal / tail tiles pay for masking
 #pragma unroll
           for (int i = 0; i < 128; ++i)
             if (i >= limit) s[i] = 0xff800000u;  // -inf
         }
-        float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-        for (int i = 0; i < 128; i += 8) {
+        for (int i = (B200_ATTN9_OVERLAP ? 64 : 0); i < 128; i += 8) {
 #pragma unroll
           for (int c = 0; c < 4; ++c)
             mx4[c] = max3n(mx4[c], __uint_as_float(s[i + 2 * c]), __uint_as_float(s[i + 2 * c + 1]));
         }
+#if B200_ATTN9_OVERLAP
+        if (any_mask) {                          // the masked path did not take the early half
+#pragma unroll
+          for (int i = 0; i < 64; i += 8) {
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+              mx4[c] = max3n(mx4[c], __uint_as_float(s[i + 2 * c]), __uint_as_float(s[i + 2 * c + 1]));
+          }
+        }
+#endif
         const float m_tile = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * p.scale_log2;
         // The reference max is ONE sequence over the tiles of an item: tile j starts from what tile j-1 (the other
         // group's thread of the same row) settled on.  That hand-off is the only coupling between the two groups.
@@ -552,6 +582,9 @@ attention_fwd9_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
           }
           sum2[i & 1] = add_f32x2(sum2[i & 1], pack_f32x2(p0, p1));
           s[i] = pack_bf16x2(p0, p1);            // keys (2i, 2i+1): low half = even key
+#if B200_ATTN9_OVERLAP
+          if (i == 31) tmem_st_32x32(p_tmem, *reinterpret_cast<const uint32_t(*)[32]>(&s[0]));   // keys [0, 64) go out early
+#endif
         }
         {
           float a0, a1, b0, b1;
@@ -563,7 +596,9 @@ attention_fwd9_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         {
           const uint32_t(&pp0)[32] = *reinterpret_cast<const uint32_t(*)[32]>(&s[0]);
           const uint32_t(&pp1)[32] = *reinterpret_cast<const uint32_t(*)[32]>(&s[32]);
+#if !B200_ATTN9_OVERLAP
           tmem_st_32x32(p_tmem, pp0);
+#endif
           tmem_st_32x32(p_tmem + 32, pp1);
           tmem_wait_st();
         }

@@ -9,6 +9,7 @@ for round in 1 2; do
   for f in /tmp/libb200sl_default.so $pkg/variants/libb200sl_*.so; do
     cp $f $pkg/libb200sl.so
     echo "== $(basename $f) round $round" >> $L
+    if [ $round -eq 1 ]; then timeout 120 python tools/gpu_check.py attn --g ${G:-9} 2>&1 | grep "RESULT\|FAIL\|rror" >> $L; fi
     timeout 120 python tools/gpu_check.py attn_quick --g ${G:-9} 2>&1 | grep "QUICK\|rror" >> $L
   done
 done
