@@ -158,6 +158,36 @@ int b200_attention_fwd(const void* Q, const void* K, const void* V, void* O, int
                        int causal, void* stream);
 
 /*
+ * b200_attention_fwd that also returns lse2[B, H, Sq] (f32) = log2(sum_t exp2(log2(e) * scale * s[t])) per query row: the
+ * residual the backward needs.  Always runs the persistent kernels (attention9.cu for D = 128, attention8.cu for D = 64).
+ */
+int b200_attention_fwd_lse(const void* Q, const void* K, const void* V, void* O, float* lse2, int B, int Sq, int Sk, int H,
+                           int D, int64_t q_stride_b, int64_t q_stride_s, int64_t q_stride_h, int64_t k_stride_b,
+                           int64_t k_stride_s, int64_t k_stride_h, int64_t v_stride_b, int64_t v_stride_s,
+                           int64_t v_stride_h, int64_t o_stride_b, int64_t o_stride_s, int64_t o_stride_h, float scale,
+                           int causal, void* stream);
+
+/*
+ * Attention backward: dQ, dK, dV of O = softmax(scale Q K^T [+ causal mask]) V given dO, O and the forward's lse2 --
+ * the part of jax.grad through FlaxAttention.__call__ (case6_attention.py:121-135) that the reference's train_step runs
+ * (case6_attention.py:206-220).  Layouts as in b200_attention_fwd; strides (elements) for
+ * q, k, v, o, dO, dQ, dK, dV as (batch, seq, head) triples in that order; dQ must be contiguous [B, Sq, H, D].
+ * workspace: f32, B*Sq*H*D + B*H*Sq elements (dQ accumulator + row sums of dO*O), caller-provided.
+ * P and dS are rounded to bf16 before the tensor-core products (as the forward rounds P); accumulation is f32.
+ */
+typedef struct {
+  const void *Q, *K, *V, *O, *dO;
+  const float* lse2;
+  void *dQ, *dK, *dV;
+  float* workspace;
+  int B, Sq, Sk, H, D;
+  int64_t strides[24];
+  float scale;
+  int causal;
+} b200_attention_bwd_args;
+int b200_attention_bwd(const b200_attention_bwd_args* args, void* stream);
+
+/*
  * optax.adam update of one f32 parameter tensor, in place (scale_by_adam, then scale(-lr), then apply_updates):
  *   mu = b1 mu + (1-b1) g;  nu = b2 nu + (1-b2) g^2;
  *   param -= lr * (mu / (1 - b1^step)) / (sqrt(nu / (1 - b2^step)) + eps)

@@ -38,6 +38,8 @@ EXPORTED_SYMBOLS = (
     "b200_cast_bf16_to_f32",
     "b200_sum_partials_to_bf16",
     "b200_adam_step",
+    "b200_attention_fwd_lse",
+    "b200_attention_bwd",
     "b200_comm_unique_id",
     "b200_mesh_create",
     "b200_mesh_axis_comm",
@@ -69,6 +71,15 @@ class GemmArgs(ctypes.Structure):
                 ("out_dtype", ctypes.c_int), ("c_block_ptrs", ctypes.c_void_p), ("m_rows_per_block", ctypes.c_int),
                 ("m_block_rot", ctypes.c_int), ("M", ctypes.c_int), ("N", ctypes.c_int), ("K", ctypes.c_int),
                 ("epilogue", ctypes.c_int), ("a_layout", ctypes.c_int)]
+
+
+class AttentionBwdArgs(ctypes.Structure):
+    """b200_attention_bwd_args of include/b200_sharded.h."""
+    _fields_ = [("Q", ctypes.c_void_p), ("K", ctypes.c_void_p), ("V", ctypes.c_void_p), ("O", ctypes.c_void_p),
+                ("dO", ctypes.c_void_p), ("lse2", ctypes.c_void_p), ("dQ", ctypes.c_void_p), ("dK", ctypes.c_void_p),
+                ("dV", ctypes.c_void_p), ("workspace", ctypes.c_void_p), ("B", ctypes.c_int), ("Sq", ctypes.c_int),
+                ("Sk", ctypes.c_int), ("H", ctypes.c_int), ("D", ctypes.c_int), ("strides", ctypes.c_int64 * 24),
+                ("scale", ctypes.c_float), ("causal", ctypes.c_int)]
 
 
 class B200Error(RuntimeError):
@@ -106,6 +117,8 @@ def load():
     lib.b200_sum_bf16_partials.argtypes = [vp, i64, i32, vp, i64, vp, i64, vp]
     lib.b200_gemm_f32.argtypes = [vp, i64, i64, vp, i64, i64, vp, i64, i64, i32, i32, i32, i32, i32, vp]
     lib.b200_attention_fwd.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32] + [i64] * 12 + [f32, i32, vp]
+    lib.b200_attention_fwd_lse.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32] + [i64] * 12 + [f32, i32, vp]
+    lib.b200_attention_bwd.argtypes = [ctypes.POINTER(AttentionBwdArgs), vp]
     lib.b200_ffn_fwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp]
     lib.b200_cast_f32_to_bf16.argtypes = [vp, vp, i64, vp]
     lib.b200_cast_bf16_to_f32.argtypes = [vp, vp, i64, vp]
@@ -320,6 +333,54 @@ def attention_fwd(q, k, v, *, scale=None, causal=False, out=None):
             float(scale), int(bool(causal)), _stream(q))
     _check(rc, "b200_attention_fwd")
     return out
+
+
+def attention_fwd_lse(q, k, v, *, scale=None, causal=False):
+    """attention_fwd that also returns lse2 [B,H,Sq] f32 (log2 of the softmax denominator, scale included): (out, lse2)."""
+    _require_cuda(q, k, v)
+    B, Sq, H, D = q.shape
+    Sk = k.shape[1]
+    out = torch.empty((B, Sq, H, D), dtype=torch.bfloat16, device=q.device)
+    lse = torch.empty((B, H, Sq), dtype=torch.float32, device=q.device)
+    if scale is None:
+        scale = D ** -0.5
+    with torch.cuda.device(q.device):
+        rc = load().b200_attention_fwd_lse(
+            _ptr(q), _ptr(k), _ptr(v), _ptr(out), _ptr(lse), B, Sq, Sk, H, D,
+            q.stride(0), q.stride(1), q.stride(2), k.stride(0), k.stride(1), k.stride(2),
+            v.stride(0), v.stride(1), v.stride(2), out.stride(0), out.stride(1), out.stride(2),
+            float(scale), int(bool(causal)), _stream(q))
+    _check(rc, "b200_attention_fwd_lse")
+    return out, lse
+
+
+def attention_bwd(q, k, v, o, do, lse2, *, scale=None, causal=False):
+    """(dq, dk, dv) of attention_fwd for the cotangent ``do`` (b200_attention_bwd); o and lse2 from attention_fwd_lse."""
+    _require_cuda(q, k, v, o, do, lse2)
+    for t in (q, k, v, o, do):
+        if t.dtype != torch.bfloat16 or t.dim() != 4 or t.stride(3) != 1:
+            raise B200Error("attention_bwd takes 4-D bf16 tensors [B,S,H,D] with contiguous D")
+    B, Sq, H, D = q.shape
+    Sk = k.shape[1]
+    if scale is None:
+        scale = D ** -0.5
+    dq = torch.empty((B, Sq, H, D), dtype=torch.bfloat16, device=q.device)
+    dk = torch.empty((B, Sk, H, D), dtype=torch.bfloat16, device=q.device)
+    dv = torch.empty((B, Sk, H, D), dtype=torch.bfloat16, device=q.device)
+    ws = torch.empty((B * Sq * H * D + B * H * Sq,), dtype=torch.float32, device=q.device)
+    a = AttentionBwdArgs()
+    a.Q, a.K, a.V, a.O, a.dO = q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), do.data_ptr()
+    a.lse2, a.dQ, a.dK, a.dV, a.workspace = lse2.data_ptr(), dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), ws.data_ptr()
+    a.B, a.Sq, a.Sk, a.H, a.D = B, Sq, Sk, H, D
+    st = []
+    for t in (q, k, v, o, do, dq, dk, dv):
+        st += [t.stride(0), t.stride(1), t.stride(2)]
+    a.strides = (ctypes.c_int64 * 24)(*st)
+    a.scale, a.causal = float(scale), int(bool(causal))
+    with torch.cuda.device(q.device):
+        rc = load().b200_attention_bwd(ctypes.byref(a), _stream(q))
+    _check(rc, "b200_attention_bwd")
+    return dq, dk, dv
 
 
 def ffn_fwd(x, w1, b1, w2, b2, *, act=EPI_BIAS_GELU_TANH, h=None, out=None, out_dtype=torch.bfloat16):

@@ -361,6 +361,7 @@ int attention_fwd9_dispatch(const void* Q, const void* K, const void* V, void* O
 // 8 = v7 as a persistent kernel (one CTA per SM walks a static work list, items overlap);
 // 9 = v8 on CTA pairs (cta_group::2 MMAs, K / V tiles loaded once per 256 query rows), head dim 128 only
 static int g_attn_variant = 0;
+thread_local float* tl_attn_lse = nullptr;
 
 }  // namespace b200
 
@@ -379,11 +380,11 @@ extern "C" int b200_attention_set_variant(int variant) {
   return B200_OK;
 }
 
-extern "C" int b200_attention_fwd(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H,
-                                  int D, int64_t q_stride_b, int64_t q_stride_s, int64_t q_stride_h,
-                                  int64_t k_stride_b, int64_t k_stride_s, int64_t k_stride_h, int64_t v_stride_b,
-                                  int64_t v_stride_s, int64_t v_stride_h, int64_t o_stride_b, int64_t o_stride_s,
-                                  int64_t o_stride_h, float scale, int causal, void* stream) {
+static int attention_fwd_common(const void* Q, const void* K, const void* V, void* O, float* lse, int B, int Sq, int Sk, int H,
+                                int D, int64_t q_stride_b, int64_t q_stride_s, int64_t q_stride_h,
+                                int64_t k_stride_b, int64_t k_stride_s, int64_t k_stride_h, int64_t v_stride_b,
+                                int64_t v_stride_s, int64_t v_stride_h, int64_t o_stride_b, int64_t o_stride_s,
+                                int64_t o_stride_h, float scale, int causal, void* stream) {
   B200_REQUIRE(Q && K && V && O, "b200_attention_fwd: null operand pointer");
   B200_REQUIRE(B > 0 && Sq > 0 && Sk > 0 && H > 0, "b200_attention_fwd: B, Sq, Sk, H must be positive");
   B200_REQUIRE(D == 64 || D == 128, "b200_attention_fwd: head dim must be 64 or 128 (got %d)", D);
@@ -397,6 +398,15 @@ extern "C" int b200_attention_fwd(const void* Q, const void* K, const void* V, v
                 reinterpret_cast<uintptr_t>(O)) % 16 == 0,
                "b200_attention_fwd: operands must be 16-byte aligned");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (lse != nullptr) {
+    // the row log-sum-exp is written by the persistent kernels' epilogue: pairs for head dim 128, single CTAs for 64
+    tl_attn_lse = lse;
+    const int rc = (D == 128 && g_attn_variant != 8)
+                       ? attention_fwd9_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st)
+                       : attention_fwd8_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
+    tl_attn_lse = nullptr;
+    return rc;
+  }
   if (g_attn_variant == 9) return attention_fwd9_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
   if (g_attn_variant == 8) return attention_fwd8_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
   if (g_attn_variant == 7) return attention_fwd7_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
@@ -426,4 +436,27 @@ extern "C" int b200_attention_fwd(const void* Q, const void* K, const void* V, v
   p.num_q_tiles = (Sq + kAttnBM - 1) / kAttnBM;
   if (D == 64) return launch_attention<64>(Q, K, V, p, B, Sq, Sk, H, strides, strides + 3, strides + 6, st);
   return launch_attention<128>(Q, K, V, p, B, Sq, Sk, H, strides, strides + 3, strides + 6, st);
+}
+
+extern "C" int b200_attention_fwd(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H,
+                                  int D, int64_t q_stride_b, int64_t q_stride_s, int64_t q_stride_h,
+                                  int64_t k_stride_b, int64_t k_stride_s, int64_t k_stride_h, int64_t v_stride_b,
+                                  int64_t v_stride_s, int64_t v_stride_h, int64_t o_stride_b, int64_t o_stride_s,
+                                  int64_t o_stride_h, float scale, int causal, void* stream) {
+  return attention_fwd_common(Q, K, V, O, nullptr, B, Sq, Sk, H, D, q_stride_b, q_stride_s, q_stride_h, k_stride_b, k_stride_s,
+                              k_stride_h, v_stride_b, v_stride_s, v_stride_h, o_stride_b, o_stride_s, o_stride_h, scale, causal,
+                              stream);
+}
+
+// b200_attention_fwd that also returns, per (batch, head, query row), lse2 = log2(sum_t exp2(log2(e) * scale * s[t])) in
+// lse2[B, H, Sq] (f32): what the backward needs to rebuild the probabilities without the running max.
+extern "C" int b200_attention_fwd_lse(const void* Q, const void* K, const void* V, void* O, float* lse2, int B, int Sq, int Sk,
+                                      int H, int D, int64_t q_stride_b, int64_t q_stride_s, int64_t q_stride_h,
+                                      int64_t k_stride_b, int64_t k_stride_s, int64_t k_stride_h, int64_t v_stride_b,
+                                      int64_t v_stride_s, int64_t v_stride_h, int64_t o_stride_b, int64_t o_stride_s,
+                                      int64_t o_stride_h, float scale, int causal, void* stream) {
+  B200_REQUIRE(lse2, "b200_attention_fwd_lse: null lse2");
+  return attention_fwd_common(Q, K, V, O, lse2, B, Sq, Sk, H, D, q_stride_b, q_stride_s, q_stride_h, k_stride_b, k_stride_s,
+                              k_stride_h, v_stride_b, v_stride_s, v_stride_h, o_stride_b, o_stride_s, o_stride_h, scale, causal,
+                              stream);
 }

@@ -61,6 +61,7 @@ struct Attn8Params {
   int H;
   int items_per_head;   // query tiles (non-causal) or pairs of query tiles (causal) per (batch, head)
   int total_items;      // items_per_head * H * B
+  float* lse;           // optional [B, H, Sq] f32: log2 of the softmax denominator per row, scale included (for the backward)
 };
 
 // Walks this CTA's work list; every role runs the same walk, so the item / tile counters agree without communication.
@@ -426,6 +427,8 @@ attention_fwd8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         mbar_wait(&pv_done[Tl & 1], (Tl >> 1) & 1);
         tc_fence_after();
         const float inv_l = 1.0f / l_sum;
+        if (p.lse != nullptr && grp == 0 && f < p.Sq)
+          p.lse[(static_cast<int64_t>(wk.batch) * p.H + wk.head) * p.Sq + f] = m_final + log2f(l_sum);
         uint32_t r[D / 2];
 #pragma unroll
         for (int c = 0; c < D / 64; ++c) {
@@ -489,6 +492,8 @@ static int launch_attention8(const void* Q, const void* K, const void* V, const 
   return B200_OK;
 }
 
+extern thread_local float* tl_attn_lse;   // set by b200_attention_fwd_lse around the dispatch
+
 int attention_fwd8_dispatch(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
                             const int64_t* strides, float scale, int causal, cudaStream_t stream) {
   Attn8Params p = {};
@@ -506,6 +511,7 @@ int attention_fwd8_dispatch(const void* Q, const void* K, const void* V, void* O
   const long long total = static_cast<long long>(p.items_per_head) * H * B;
   if (total > 0x7fffffffLL) return fail(B200_ERR_INVALID_ARGUMENT, "b200_attention_fwd: too many work items");
   p.total_items = static_cast<int>(total);
+  p.lse = tl_attn_lse;
   if (D == 64) return launch_attention8<64>(Q, K, V, p, B, Sq, Sk, H, strides, strides + 3, strides + 6, stream);
   return launch_attention8<128>(Q, K, V, p, B, Sq, Sk, H, strides, strides + 3, strides + 6, stream);
 }

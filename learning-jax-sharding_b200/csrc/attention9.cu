@@ -77,6 +77,7 @@ struct Attn9Params {
   int num_q_blocks;     // 256-row query blocks per (batch, head)
   int items_per_head;   // query blocks (non-causal) or pairs of query blocks (causal) per (batch, head)
   int total_items;      // items_per_head * H * B
+  float* lse;           // optional [B, H, Sq] f32: log2 of the softmax denominator per row, scale included (for the backward)
   long long* prof;      // bring-up aid (B200_ATTN_PROFILE builds): softmax warp 4 of block 0 -> [0..7], MMA warp -> [8..10]
 };
 
@@ -622,6 +623,8 @@ attention_fwd9_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         mbar_wait(&pv_done[Tl & 1], (Tl >> 1) & 1);
         tc_fence_after();
         const float inv_l = 1.0f / l_sum;
+        if (p.lse != nullptr && grp == 0 && f < p.Sq)
+          p.lse[(static_cast<int64_t>(wk.batch) * p.H + wk.head) * p.Sq + f] = m_final + log2f(l_sum);
         uint32_t r[D / 2];
 #pragma unroll
         for (int c = 0; c < D / 64; ++c) {
@@ -704,6 +707,8 @@ static int launch_attention9(const void* Q, const void* K, const void* V, const 
 
 extern long long* g_attn_prof;
 
+extern thread_local float* tl_attn_lse;   // set by b200_attention_fwd_lse around the dispatch
+
 int attention_fwd9_dispatch(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
                             const int64_t* strides, float scale, int causal, cudaStream_t stream) {
   Attn9Params p = {};
@@ -722,6 +727,7 @@ int attention_fwd9_dispatch(const void* Q, const void* K, const void* V, void* O
   const long long total = static_cast<long long>(p.items_per_head) * H * B;
   if (total > 0x7fffffffLL) return fail(B200_ERR_INVALID_ARGUMENT, "b200_attention_fwd: too many work items");
   p.total_items = static_cast<int>(total);
+  p.lse = tl_attn_lse;
   p.prof = g_attn_prof;
   if (D != 128) return fail(B200_ERR_INVALID_ARGUMENT, "attention variant 9 (CTA pairs) needs head dim 128");
   return launch_attention9<128>(Q, K, V, p, B, Sq, Sk, H, strides, strides + 3, strides + 6, stream);

@@ -455,3 +455,41 @@ def test_dense_train_step_literal_case5(ljs, wspec):
     # forward with the updated parameters still matches the oracle's forward
     y = ljs.nn.dense(x, state.params["kernel"])
     torch.testing.assert_close(y.global_array().cpu().float(), rm.dense_bf16(x_host, k).float(), **BF16_TOL)
+
+
+# ------------------------------------------------------------------------------ attention backward (8f row 1)
+GRAD_TOL = dict(rtol=3e-2, atol=3e-2)
+
+
+@pytest.mark.parametrize("shape", [(1, 128, 128, 1, 64), (1, 128, 128, 1, 128), (2, 256, 256, 2, 128), (1, 200, 333, 2, 64),
+                                   (1, 384, 640, 2, 128), (2, 1024, 1024, 2, 128)])
+@pytest.mark.parametrize("causal", [False, True])
+def test_attention_backward_matches_oracle(ljs, shape, causal):
+    """dQ, dK, dV (b200_attention_bwd) and the forward's lse2 (b200_attention_fwd_lse) against autodiff of the f64
+    formula; cotangent and inputs seeded, shapes ragged in Sq / Sk."""
+    B, Sq, Sk, H, D = shape
+    q = rm.synthetic((B, Sq, H, D), 90).to(torch.bfloat16)
+    k = rm.synthetic((B, Sk, H, D), 91).to(torch.bfloat16)
+    v = rm.synthetic((B, Sk, H, D), 92).to(torch.bfloat16)
+    do = rm.synthetic((B, Sq, H, D), 93).to(torch.bfloat16)
+    dq_w, dk_w, dv_w, lse_w = rm.attention_core_grads(q, k, v, do, causal=causal)
+    o, lse = ljs.capi.attention_fwd_lse(_dev(q), _dev(k), _dev(v), causal=causal)
+    torch.testing.assert_close(o.cpu().float(), rm.attention_core(q, k, v, causal=causal).float(), **BF16_TOL)
+    torch.testing.assert_close(lse.cpu(), lse_w, rtol=1e-3, atol=2e-2)
+    dq, dk, dv = ljs.capi.attention_bwd(_dev(q), _dev(k), _dev(v), o, _dev(do), lse, causal=causal)
+    torch.testing.assert_close(dv.cpu().float(), dv_w.float(), **GRAD_TOL)
+    torch.testing.assert_close(dk.cpu().float(), dk_w.float(), **GRAD_TOL)
+    torch.testing.assert_close(dq.cpu().float(), dq_w.float(), **GRAD_TOL)
+
+
+def test_attention_backward_properties(ljs):
+    """Size-independent checks at a larger shape: uniform V makes dQ and dK vanish (softmax rows sum to one, so O does not
+    depend on the scores), and dV's column sums equal dO's column sums per (batch, head)."""
+    B, S, H, D = 2, 2048, 4, 128
+    q, k = (torch.randn(B, S, H, D, generator=torch.Generator().manual_seed(i)).to(torch.bfloat16).cuda() for i in (1, 2))
+    do = torch.randn(B, S, H, D, generator=torch.Generator().manual_seed(3)).to(torch.bfloat16).cuda()
+    v = torch.full((B, S, H, D), 0.5, dtype=torch.bfloat16, device="cuda")
+    o, lse = ljs.capi.attention_fwd_lse(q, k, v)
+    dq, dk, dv = ljs.capi.attention_bwd(q, k, v, o, do, lse)
+    assert dq.float().abs().max().item() < 2e-2 and dk.float().abs().max().item() < 2e-2
+    torch.testing.assert_close(dv.float().sum(1), do.float().sum(1), rtol=2e-2, atol=0.5)
