@@ -6,8 +6,9 @@
 Host mirror of the pieces the script names: ``adam`` (optax.adam), ``TrainState.create / apply_gradients``
 (flax.training.train_state), and ``dense_sum_loss_grad`` (the kernel gradient jax.grad produces for that loss).  The
 arithmetic runs in the library: the weight-gradient product x^T . dy is b200_gemm_bf16_ex with a_layout = B200_A_KM
-(tcgen05, MN-major A tiles through TMA, no transposed copy), the update is b200_adam_step.  The backward of the attention
-module (case6_attention.py:206-220) is not built yet.
+(tcgen05, MN-major A tiles through TMA, no transposed copy), the update is b200_adam_step.  For the attention module
+(case6_attention.py:206-220) the kernels exist (capi.attention_fwd_lse / capi.attention_bwd, the Dense backward GEMMs); the
+module-level chaining over the sharded state is not built yet.
 """
 from __future__ import annotations
 

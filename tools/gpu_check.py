@@ -374,6 +374,21 @@ def main():
         gb = g.to(torch.bfloat16)
         ms4 = time_fn(lambda: capi.adam_step(p, gb, mu, nu, step=3), iters=20, warmup=3)
         print(f"  adam_step n={n} (bf16 grad): {ms4:.4f} ms {26.0 * n / ms4 / 1e6:.0f} GB/s (26 B per element)", flush=True)
+    elif args.what == "attn_bwd_time":
+        # backward of the attention core at the case5 shape, against torch SDPA's (cuDNN / flash) backward
+        for (B, S, H, D, causal) in [(8, 4096, 32, 128, False), (8, 4096, 32, 128, True), (8, 4096, 32, 64, False)]:
+            q, k, v, do = (torch.randn(B, S, H, D, device="cuda").to(torch.bfloat16) for _ in range(4))
+            o, lse = capi.attention_fwd_lse(q, k, v, causal=causal)
+            ms = time_fn(lambda: capi.attention_bwd(q, k, v, o, do, lse, causal=causal), iters=5, warmup=2)
+            fl = 2.5 * ((2.0 * B * H * S * (S + 1) * D) if causal else 4.0 * B * H * S * S * D)   # 5 matmuls vs the forward's 2
+            print(f"  attn bwd B={B} S={S} H={H} D={D} causal={causal}: {ms:.3f} ms {fl / ms / 1e9:.1f} TFLOP/s", flush=True)
+            qt, kt, vt = (t.transpose(1, 2).detach().requires_grad_(True) for t in (q, k, v))
+            ot = torch.nn.functional.scaled_dot_product_attention(qt, kt, vt, is_causal=causal)
+            dot = do.transpose(1, 2)
+            def sdpa_bwd():
+                torch.autograd.grad(ot, (qt, kt, vt), dot, retain_graph=True)
+            ms2 = time_fn(sdpa_bwd, iters=5, warmup=2)
+            print(f"    torch sdpa backward: {ms2:.3f} ms {fl / ms2 / 1e9:.1f} TFLOP/s", flush=True)
     elif args.what == "attn_quick":
         # one line per call, for A/B runs of library variants: burst (5 iterations) non-causal / causal and a sustained
         # run (300 launches) with the NVML clock, all at B8 S4096 H32 D128
