@@ -7,17 +7,20 @@
 //   dP = dO_i V_j^T           (MMA 2)                                    dS = scale P (dP - delta_i)            lse from the fwd)
 //   dV_j += P^T dO_i          (MMA 3: A = P from smem read MN-major, i.e. transposed for free)
 //   dK_j += dS^T Q_i          (MMA 4, same trick)
-//   dQ_i += dS K_j            (MMA 5: per-step result, added to an f32 dQ accumulator in global memory with vector reds)
+//   dQ_i += dS K_j            (MMA 5: per-step result, staged through the P / dS buffers and added to an f32 dQ
+//                              accumulator in global memory by TMA reduce-add: per-thread vector reds cost 36 % of the time)
 // with delta_i = rowsum(dO_i * O_i) from a small pre-pass.  P and dS go through shared memory as bf16, stored row-major
 // [query][key] in 128-byte-swizzled 64-key chunks: that one image is K-major for dS (dQ = dS K) and MN-major for its
 // transpose (dV = P^T dO, dK = dS^T Q).  Tensor memory: S | dP | dV | dK (4 x 128 columns); dQ reuses S's columns once the
-// softmax warps have read S.  Everything is single-buffered: correct first, the pipelining of the forward kernels is the
-// next step (DESIGN.md section 4.6 has the measured rate).
+// compute warps have read S.  Shared memory (D = 128): K_j, V_j, Q_i, 2 x dO_i, P, dS = 7 x 32 KB.  dO is double-buffered so
+// that dP of the next step (which needs neither S's columns nor Q) runs under the dQ read-out and the Q load of that step
+// (DESIGN.md section 4.6 has the measured rates of this and of the single-buffered first version).
 //
-//   warp 0   TMA producer: K_j, V_j once; Q_i, dO_i per step
+//   warp 0   TMA producer: K_j, V_j once; dO_i one step ahead, Q_i per step
 //   warp 1   MMA issuer
 //   warp 2   TMEM allocator
-//   warps 4..7  one thread per query row: P, dS, the dQ reduction, and at the end dK / dV -> global
+//   warps 4..11 two threads per query row (keys [0,64) and [64,128) of the tile; D/2 columns each of dQ, dK, dV):
+//               P, dS, the dQ reduction, and at the end dK / dV -> global
 #include <cuda.h>
 #include <math.h>
 
@@ -28,20 +31,20 @@ namespace b200 {
 
 constexpr int kBwBM = 128;      // query rows per step
 constexpr int kBwBN = 128;      // keys per CTA
-constexpr int kBwThreads = 256;
+constexpr int kBwThreads = 384;
 
 template <int D>
 struct AttnBwdCfg {
   static constexpr int kTileBytes = 128 * D * 2;          // one of K_j, V_j, Q_i, dO_i
   static constexpr int kPBytes = kBwBM * kBwBN * 2;       // P or dS as bf16
-  static constexpr int kSmemBytes = 4 * kTileBytes + 2 * kPBytes + 1024 + 256;
+  static constexpr int kSmemBytes = 5 * kTileBytes + 2 * kPBytes + 1024 + 256;
   static constexpr int kSCol = 0, kDPCol = 128, kDVCol = 256, kDKCol = 384;
 };
 
 struct AttnBwdParams {
   const float* lse2;      // [B, H, Sq]
   const float* delta;     // [B, H, Sq]
-  float* dq_acc;          // [B, Sq, H, D] f32, zeroed by the caller of the kernel
+  float* dq_acc;          // [B, Sq, H, D] f32, zeroed by the caller of the kernel (written through tmDQ)
   __nv_bfloat16 *dK, *dV; // [B, Sk, H, D]
   int Sq, Sk, H;
   int64_t dk_stride_b, dk_stride_s, dk_stride_h, dv_stride_b, dv_stride_s, dv_stride_h;
@@ -50,35 +53,33 @@ struct AttnBwdParams {
   int num_q_tiles;
 };
 
-__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
-  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
-}
-__device__ __forceinline__ void bwd_group_barrier() {      // the 128 compute threads (warps 4..7)
-  asm volatile("bar.sync 2, 128;" ::: "memory");
+__device__ __forceinline__ void bwd_group_barrier() {      // the 256 compute threads (warps 4..11)
+  asm volatile("bar.sync 2, 256;" ::: "memory");
 }
 
 template <int D>
 __global__ void __launch_bounds__(kBwThreads, 1)
 attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                      const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
-                     const AttnBwdParams p) {
+                     const __grid_constant__ CUtensorMap tmDQ, const AttnBwdParams p) {
   using Cfg = AttnBwdCfg<D>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sK = smem;
   uint8_t* sV = sK + Cfg::kTileBytes;
   uint8_t* sQ = sV + Cfg::kTileBytes;
-  uint8_t* sDO = sQ + Cfg::kTileBytes;
-  uint8_t* sP = sDO + Cfg::kTileBytes;
+  uint8_t* sDO = sQ + Cfg::kTileBytes;                    // two buffers
+  uint8_t* sP = sDO + 2 * Cfg::kTileBytes;
   uint8_t* sDS = sP + Cfg::kPBytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(sDS + Cfg::kPBytes);
   uint64_t* kv_full = bars;          // TMA bytes of K_j and V_j
-  uint64_t* q_full = bars + 1;       // TMA bytes of Q_i and dO_i
-  uint64_t* step_done = bars + 2;    // MMA commit after MMAs 3-5 of a step: sQ / sDO / sP / sDS are free, dQ is in TMEM
+  uint64_t* q_full = bars + 1;       // TMA bytes of Q_i
+  uint64_t* step_done = bars + 2;    // MMA commit after MMAs 3-5 of a step: sQ / sDO[.] / sP / sDS are free, dQ is in TMEM
   uint64_t* sdp_full = bars + 3;     // MMA commit after MMAs 1-2: S and dP are in TMEM
-  uint64_t* pds_full = bars + 4;     // 4 warp arrivals: P and dS are in shared memory (S and dP have been read)
-  uint64_t* dq_free = bars + 5;      // 4 warp arrivals: dQ has been read out of S's columns
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 6);
+  uint64_t* pds_full = bars + 4;     // 8 warp arrivals: P and dS are in shared memory (S and dP have been read)
+  uint64_t* dq_free = bars + 5;      // 8 warp arrivals: dQ has been read out of S's columns
+  uint64_t* do_full = bars + 6;      // [2] TMA bytes of dO_i
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 8);
 
   const int warp = uniform_warp_idx();
   const int lane = threadIdx.x & 31;
@@ -101,8 +102,10 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     mbar_init(q_full, 1);
     mbar_init(step_done, 1);
     mbar_init(sdp_full, 1);
-    mbar_init(pds_full, 4);
-    mbar_init(dq_free, 4);
+    mbar_init(pds_full, 8);
+    mbar_init(dq_free, 8);
+    mbar_init(&do_full[0], 1);
+    mbar_init(&do_full[1], 1);
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc<512>(tmem_ptr_smem);
@@ -120,15 +123,25 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         tma_load_4d(sK + c * (128 * 128), &tmK, kv_full, c * 64, head, t0, batch);
         tma_load_4d(sV + c * (128 * 128), &tmV, kv_full, c * 64, head, t0, batch);
       }
-      for (int s = 0; s < nsteps; ++s) {
-        const int f0 = (i_start + s) * kBwBM;
-        if (s > 0) mbar_wait(step_done, (s - 1) & 1);
-        mbar_arrive_expect_tx(q_full, 2 * Cfg::kTileBytes);
+      auto load_do = [&](int st) {
+        uint8_t* dst = sDO + (st & 1) * Cfg::kTileBytes;
+        mbar_arrive_expect_tx(&do_full[st & 1], Cfg::kTileBytes);
 #pragma unroll
-        for (int c = 0; c < D / 64; ++c) {
-          tma_load_4d(sQ + c * (128 * 128), &tmQ, q_full, c * 64, head, f0, batch);
-          tma_load_4d(sDO + c * (128 * 128), &tmDO, q_full, c * 64, head, f0, batch);
-        }
+        for (int c = 0; c < D / 64; ++c)
+          tma_load_4d(dst + c * (128 * 128), &tmDO, &do_full[st & 1], c * 64, head, (i_start + st) * kBwBM, batch);
+      };
+      auto load_q = [&](int st) {
+        mbar_arrive_expect_tx(q_full, Cfg::kTileBytes);
+#pragma unroll
+        for (int c = 0; c < D / 64; ++c)
+          tma_load_4d(sQ + c * (128 * 128), &tmQ, q_full, c * 64, head, (i_start + st) * kBwBM, batch);
+      };
+      load_do(0);
+      load_q(0);
+      for (int s = 0; s + 1 < nsteps; ++s) {
+        load_do(s + 1);                       // its buffer was last read in step s-1, whose step_done was waited for below
+        mbar_wait(step_done, s & 1);          // MMAs 3-5 of step s are done with sQ
+        load_q(s + 1);
       }
     }
     __syncwarp();
@@ -138,11 +151,11 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     constexpr uint32_t idesc_t = make_idesc_bf16(128, D, true, true);         // dV, dK: A = (P | dS)^T, B = dO | Q
     constexpr uint32_t idesc_q = make_idesc_bf16(128, D, false, true);        // dQ: A = dS K-major, B = K MN-major
     const uint64_t q_k = make_smem_desc_sw128(smem_u32(sQ), 16, 1024);        // K-major views ([row][d])
-    const uint64_t do_k = make_smem_desc_sw128(smem_u32(sDO), 16, 1024);
+    const uint64_t do_k0 = make_smem_desc_sw128(smem_u32(sDO), 16, 1024);
     const uint64_t k_k = make_smem_desc_sw128(smem_u32(sK), 16, 1024);
     const uint64_t v_k = make_smem_desc_sw128(smem_u32(sV), 16, 1024);
     const uint64_t q_mn = make_smem_desc_sw128(smem_u32(sQ), 128 * 128, 1024);   // MN-major views ([k = row][n = d])
-    const uint64_t do_mn = make_smem_desc_sw128(smem_u32(sDO), 128 * 128, 1024);
+    const uint64_t do_mn0 = make_smem_desc_sw128(smem_u32(sDO), 128 * 128, 1024);
     const uint64_t k_mn = make_smem_desc_sw128(smem_u32(sK), 128 * 128, 1024);
     const uint64_t p_mn = make_smem_desc_sw128(smem_u32(sP), 128 * 128, 1024);   // P^T: [k = query][m = key]
     const uint64_t ds_mn = make_smem_desc_sw128(smem_u32(sDS), 128 * 128, 1024);
@@ -151,19 +164,27 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     const uint32_t t_dv = tmem_base + Cfg::kDVCol, t_dk = tmem_base + Cfg::kDKCol;
     mbar_wait(kv_full, 0);
     for (int s = 0; s < nsteps; ++s) {
-      mbar_wait(q_full, s & 1);
-      if (s > 0) mbar_wait(dq_free, (s - 1) & 1);       // S's columns still hold dQ of the previous step until then
+      const uint64_t do_k = desc_advance(do_k0, (s & 1) * Cfg::kTileBytes);
+      const uint64_t do_mn = desc_advance(do_mn0, (s & 1) * Cfg::kTileBytes);
+      // dP first: it needs neither Q_i nor S's columns (which hold dQ of the previous step until it has been read out)
+      mbar_wait(&do_full[s & 1], (s >> 1) & 1);
       tc_fence_after();
       if (elect_one()) {
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk) {           // contraction over the head dim, 64-wide chunks 16 KB apart
           const uint32_t o = (kk >> 2) * (128 * 128) + (kk & 3) * 32;
-          mma_bf16_ss(t_s, desc_advance(q_k, o), desc_advance(k_k, o), idesc_s, kk > 0);
+          mma_bf16_ss(t_dp, desc_advance(do_k, o), desc_advance(v_k, o), idesc_s, kk > 0);
         }
+      }
+      __syncwarp();
+      mbar_wait(q_full, s & 1);
+      if (s > 0) mbar_wait(dq_free, (s - 1) & 1);
+      tc_fence_after();
+      if (elect_one()) {
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk) {
           const uint32_t o = (kk >> 2) * (128 * 128) + (kk & 3) * 32;
-          mma_bf16_ss(t_dp, desc_advance(do_k, o), desc_advance(v_k, o), idesc_s, kk > 0);
+          mma_bf16_ss(t_s, desc_advance(q_k, o), desc_advance(k_k, o), idesc_s, kk > 0);
         }
         mma_commit(sdp_full);
       }
@@ -193,6 +214,7 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
   } else if (warp >= 4) {
     // ===================== P, dS, dQ reduction, dK / dV epilogue =====================
     const int quad = warp & 3;
+    const int grp = (warp - 4) >> 2;                   // keys [64 grp, 64 grp + 64) of the tile; columns [grp D/2, +D/2) of dQ, dK, dV
     const int r = quad * 32 + lane;                    // query row of the step's tile (and key row in the epilogue)
     const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
     const int64_t bh = static_cast<int64_t>(batch) * p.H + head;
@@ -206,8 +228,13 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       if (!row_valid) limit = 0;
       mbar_wait(sdp_full, s & 1);
       tc_fence_after();
+      if (s > 0) {
+        // sP / sDS doubled as the dQ staging tile of the previous step: the TMA reduce must have read it
+        if (warp == 4 && lane == 0) tma_store_wait_read<0>();
+        bwd_group_barrier();
+      }
 #pragma unroll 1
-      for (int c = 0; c < kBwBN / 32; ++c) {
+      for (int c = 2 * grp; c < 2 * grp + 2; ++c) {
         uint32_t sv[32], dv[32];
         tmem_ld_32x32(lane_base + Cfg::kSCol + c * 32, sv);
         tmem_ld_32x32(lane_base + Cfg::kDPCol + c * 32, dv);
@@ -242,30 +269,38 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       // ---- dQ_i of this step: TMEM (S's columns) -> f32 accumulator in global memory
       mbar_wait(step_done, s & 1);
       tc_fence_after();
-      float* dq_row = p.dq_acc + ((static_cast<int64_t>(batch) * p.Sq + f) * p.H + head) * D;
+      // this thread's D/2 columns of its row -> the staging tile (f32, [32-column chunk][row][128 B], 16-byte units XOR-swizzled
+      // like the tensor map), then ONE thread hands the tile to TMA: dq_acc[b, f0.., head, :] += tile, rows past Sq clipped
 #pragma unroll 1
-      for (int c = 0; c < D / 32; ++c) {
+      for (int c = grp * (D / 64); c < (grp + 1) * (D / 64); ++c) {
         uint32_t q[32];
         tmem_ld_32x32(lane_base + Cfg::kSCol + c * 32, q);
         tmem_wait_ld();
-        if (row_valid) {
+        uint8_t* dst = sP + c * (kBwBM * 128) + r * 128;
 #pragma unroll
-          for (int k = 0; k < 32; k += 4)
-            red_add_v4(dq_row + c * 32 + k, __uint_as_float(q[k]), __uint_as_float(q[k + 1]), __uint_as_float(q[k + 2]),
-                       __uint_as_float(q[k + 3]));
-        }
+        for (int u = 0; u < 8; ++u)
+          *reinterpret_cast<uint4*>(dst + ((u ^ (r & 7)) << 4)) = make_uint4(q[4 * u], q[4 * u + 1], q[4 * u + 2], q[4 * u + 3]);
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(dq_free);
+      if (lane == 0) mbar_arrive(dq_free);             // S's columns may take the next step's scores
+      fence_async_smem();
+      bwd_group_barrier();
+      if (warp == 4 && lane == 0) {
+#pragma unroll
+        for (int c = 0; c < D / 32; ++c)
+          tma_reduce_add_4d(&tmDQ, sP + c * (kBwBM * 128), c * 32, head, (i_start + s) * kBwBM, batch);
+        tma_store_commit();
+      }
     }
+    if (warp == 4 && lane == 0) tma_store_wait_all<0>();  // the last tile has left shared memory (and landed) before the CTA exits
     // ---- dK_j, dV_j: complete after the last step's MMAs (step_done of the last step has been waited for above)
     const int t = t0 + r;
     if (nsteps > 0) {
       __nv_bfloat16* dk_row = p.dK + batch * p.dk_stride_b + static_cast<int64_t>(t) * p.dk_stride_s + head * p.dk_stride_h;
       __nv_bfloat16* dv_row = p.dV + batch * p.dv_stride_b + static_cast<int64_t>(t) * p.dv_stride_s + head * p.dv_stride_h;
 #pragma unroll 1
-      for (int c = 0; c < D / 32; ++c) {
+      for (int c = grp * (D / 64); c < (grp + 1) * (D / 64); ++c) {
         uint32_t a[32], b[32];
         tmem_ld_32x32(lane_base + Cfg::kDKCol + c * 32, a);
         tmem_ld_32x32(lane_base + Cfg::kDVCol + c * 32, b);
@@ -346,6 +381,15 @@ static int launch_attention_bwd(const void* Q, const void* K, const void* V, con
   if (rc == B200_OK) rc = make_bsnh_map(&tmV, V, B, Sk, H, D, st[6], st[7], st[8], 128);
   if (rc == B200_OK) rc = make_bsnh_map(&tmDO, dO, B, Sq, H, D, st[12], st[13], st[14], 128);
   if (rc != B200_OK) return rc;
+  CUtensorMap tmDQ;
+  {
+    uint64_t dims[4] = {static_cast<uint64_t>(D), static_cast<uint64_t>(H), static_cast<uint64_t>(Sq), static_cast<uint64_t>(B)};
+    uint64_t strides[4] = {0, static_cast<uint64_t>(D) * 4, static_cast<uint64_t>(H) * D * 4,
+                           static_cast<uint64_t>(Sq) * H * D * 4};
+    uint32_t box[4] = {32, 1, 128, 1};
+    rc = make_tensor_map(&tmDQ, p.dq_acc, 4, 4, dims, strides, box, 3);
+    if (rc != B200_OK) return rc;
+  }
   const int64_t rows = static_cast<int64_t>(B) * Sq * H;
   const int64_t blocks = (rows + 7) / 8;
   attention_delta_kernel<D><<<static_cast<int>(blocks < 148 * 8 ? blocks : 148 * 8), 256, 0, stream>>>(
@@ -357,7 +401,7 @@ static int launch_attention_bwd(const void* Q, const void* K, const void* V, con
   auto kern = attention_bwd_kernel<D>;
   B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
   dim3 grid((Sk + kBwBN - 1) / kBwBN, H, B);
-  kern<<<grid, kBwThreads, Cfg::kSmemBytes, stream>>>(tmQ, tmK, tmV, tmDO, p);
+  kern<<<grid, kBwThreads, Cfg::kSmemBytes, stream>>>(tmQ, tmK, tmV, tmDO, tmDQ, p);
   B200_CUDA_CHECK(cudaGetLastError());
   launch_counter().fetch_add(1);
   return B200_OK;
