@@ -7,8 +7,8 @@ Host mirror of the pieces the script names: ``adam`` (optax.adam), ``TrainState.
 (flax.training.train_state), and ``dense_sum_loss_grad`` (the kernel gradient jax.grad produces for that loss).  The
 arithmetic runs in the library: the weight-gradient product x^T . dy is b200_gemm_bf16_ex with a_layout = B200_A_KM
 (tcgen05, MN-major A tiles through TMA, no transposed copy), the update is b200_adam_step.  For the attention module
-(case6_attention.py:206-220) the kernels exist (capi.attention_fwd_lse / capi.attention_bwd, the Dense backward GEMMs); the
-module-level chaining over the sharded state is not built yet.
+(case6_attention.py:206-220) ``attention_train_step`` chains capi.attention_fwd_lse / capi.attention_bwd and the Dense
+backward GEMMs over the sharded state in the head-sharded layout.
 """
 from __future__ import annotations
 
@@ -110,3 +110,81 @@ def dense_sum_loss_grad(x: ShardedArray, kernel: ShardedArray) -> ShardedArray:
 def dense_train_step(state: TrainState, x: ShardedArray, name: str = "kernel") -> TrainState:
     """train_step of case5_attention_dense.py:130-139 for the single-Dense module: grads of sum(Dense(x)), then Adam."""
     return state.apply_gradients(grads={name: dense_sum_loss_grad(x, state.params[name])})
+
+
+# ------------------------------------------------------------------ the attention module (case6_attention.py:206-220)
+def attention_sum_loss_grads(module, params, x: ShardedArray) -> Dict[str, ShardedArray]:
+    """Gradients of ``module(params, x).sum()`` for ``nn.FlaxAttention(layout="heads")`` in the parameters' shardings
+    (to_q / to_k / to_v column-parallel over the model axis, to_out_0 row-parallel, batch over the data axis): what
+    ``jax.grad(loss_unrolled)`` returns in the reference's train_step (case6_attention.py:206-214) under the head-sharded
+    annotation set of BASELINE.json's case6 config.  Per device: the forward with its residuals (q, k, v, o, lse2), then
+        dO = dy . Wo^T                         (b200_gemm_bf16, b_layout = NK; dy = ones, the cotangent of .sum())
+        dWo = o^T . dy, dWq|k|v = x^T . dq|k|v (b200_gemm_bf16_ex, a_layout = KM, f32 partials)
+        dq, dk, dv                             (b200_attention_bwd)
+    and ONE collective kind: the all-reduce of the weight-gradient partials over the data axis.  Nothing crosses the model
+    axis in the backward (x and dy are replicated over it, every head's chain is local).  Keys of the result: "to_q", "to_k",
+    "to_v", "to_out_0.kernel", "to_out_0.bias"."""
+    from . import nn as _nn
+    if module.layout != "heads":
+        raise NotImplementedError("attention_sum_loss_grads covers layout='heads' (the BASELINE.json case6 annotation set)")
+    rt = _rt.get_runtime()
+    comp = _rt.local_compute()
+    mesh = x.sharding.mesh
+    w_o, b_o = params["to_out_0"]
+    for name in ("to_q", "to_k", "to_v"):
+        kw, _ = _axes(params[name])
+        if kw:
+            raise NotImplementedError(f"{name} must be column-parallel (dim 0 unsharded) in the 'heads' layout")
+    if _axes(w_o)[1]:
+        raise NotImplementedError("to_out_0 must be row-parallel (dim 1 unsharded) in the 'heads' layout")
+    H, D = module.heads, module.dim_head
+    xg = _nn.with_logical_constraint(x, ("batch", None, None))                # the sequence gathered, as in the forward
+    data_axes = tuple(_axes(xg)[0])
+    q, k, v = (_nn.dense(xg, params[n]) for n in ("to_q", "to_k", "to_v"))   # features sharded like the kernels' columns
+    q4, k4, v4 = (_nn.split_heads(t, H) for t in (q, k, v))
+    B, S, M = x.shape
+    parts = {n: {} for n in ("to_q", "to_k", "to_v", "to_out_0.kernel")}
+    for d in rt.local_device_ids:
+        ql, kl, vl = q4.shard(d), k4.shard(d), v4.shard(d)                    # [b_loc, S, H_loc, D]
+        o, lse = comp.attention_fwd_lse(ql, kl, vl, scale=module.scale, causal=module.causal)
+        rows = ql.shape[0] * S
+        dy = torch.ones((rows, M), dtype=torch.bfloat16, device=ql.device)
+        wo_l = _to_bf16(w_o.shard(d))                                         # [H_loc * D, M]
+        do = comp.gemm_bf16(dy, wo_l, b_layout=1)                             # dy . Wo^T -> [rows, H_loc * D]
+        o2 = o.reshape(rows, -1)
+        parts["to_out_0.kernel"][d] = comp.gemm_bf16_tn(o2, dy, out_dtype=torch.float32)
+        dq, dk, dv = comp.attention_bwd(ql, kl, vl, o, do.reshape(ql.shape), lse, scale=module.scale, causal=module.causal)
+        x2 = _to_bf16(xg.shard(d).reshape(rows, M))
+        for n, g in (("to_q", dq), ("to_k", dk), ("to_v", dv)):
+            parts[n][d] = comp.gemm_bf16_tn(x2, g.reshape(rows, -1), out_dtype=torch.float32)
+    grads = {}
+    for n, part in parts.items():
+        if data_axes:
+            part = rt.all_reduce(part, mesh.axis_groups(data_axes))           # the data-parallel gradient reduction
+        part = {d: comp.cast_bf16_to_f32(comp.cast_f32_to_bf16(t.contiguous())) for d, t in part.items()}
+        target = w_o if n == "to_out_0.kernel" else params[n]
+        grads[n] = ShardedArray(target.shape, torch.float32, target.sharding, part)
+    # d sum(y) / d bias = number of (batch, position) rows, in the bias's dtype chain (bf16) like the oracle
+    nrows = float(torch.tensor(float(B * S)).to(torch.bfloat16))
+    grads["to_out_0.bias"] = ShardedArray(b_o.shape, torch.float32, b_o.sharding,
+                                          {d: torch.full_like(t, nrows, dtype=torch.float32) for d, t in b_o.local_shards.items()})
+    return grads
+
+
+def attention_train_state(module, params, tx: Adam) -> TrainState:
+    """TrainState over the module's parameters with the flat names attention_sum_loss_grads uses."""
+    w_o, b_o = params["to_out_0"]
+    flat = {"to_q": params["to_q"], "to_k": params["to_k"], "to_v": params["to_v"], "to_out_0.kernel": w_o,
+            "to_out_0.bias": b_o}
+    return TrainState.create(apply_fn=module, params=flat, tx=tx)
+
+
+def attention_params_of(state: TrainState):
+    """The nested parameter dict nn.FlaxAttention.__call__ takes, from a TrainState built by attention_train_state."""
+    p = state.params
+    return {"to_q": p["to_q"], "to_k": p["to_k"], "to_v": p["to_v"], "to_out_0": (p["to_out_0.kernel"], p["to_out_0.bias"])}
+
+
+def attention_train_step(module, state: TrainState, x: ShardedArray) -> TrainState:
+    """train_step of case6_attention.py:206-220: grads of ``module(params, x).sum()``, then ``state.apply_gradients``."""
+    return state.apply_gradients(grads=attention_sum_loss_grads(module, attention_params_of(state), x))

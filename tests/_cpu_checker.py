@@ -76,3 +76,14 @@ def adam_step(param, grad, mu, nu, *, step, lr=1e-3, b1=0.9, b2=0.999, eps=1e-8)
     mu.copy_(mu2)
     nu.copy_(nu2)
     return param
+
+
+def attention_fwd_lse(q, k, v, *, scale=None, causal=False):
+    o = rm.attention_core(q, k, v, scale, causal)
+    _, _, _, lse = rm.attention_core_grads(q, k, v, torch.zeros_like(q), scale, causal)
+    return o, lse
+
+
+def attention_bwd(q, k, v, o, do, lse2, *, scale=None, causal=False):
+    dq, dk, dv, _ = rm.attention_core_grads(q, k, v, do, scale, causal)
+    return dq, dk, dv

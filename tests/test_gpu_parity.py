@@ -493,3 +493,32 @@ def test_attention_backward_properties(ljs):
     dq, dk, dv = ljs.capi.attention_bwd(q, k, v, o, do, lse)
     assert dq.float().abs().max().item() < 2e-2 and dk.float().abs().max().item() < 2e-2
     torch.testing.assert_close(dv.float().sum(1), do.float().sum(1), rtol=2e-2, atol=0.5)
+
+
+@pytest.mark.parametrize("causal", [False, True])
+def test_attention_module_train_step_literal_size(ljs, causal):
+    """train_step of the attention module (case6_attention.py:206-220) at the script's literal size (x (8,256,640), 8 heads x
+    64) in the head-sharded layout on four virtual devices of one GPU: gradients in the parameters' shardings against autodiff
+    of the unsharded f64 formula, then one Adam step through b200_adam_step."""
+    ljs.init_virtual(4, "cuda:0")
+    mesh = ljs.Mesh(ljs.create_device_mesh((2, 2)), ("data", "model"))
+    model = ljs.nn.FlaxAttention(640, heads=8, dim_head=64, causal=causal, layout="heads")
+    host = model.init_host(seed=1)
+    host["to_out_0"] = (host["to_out_0"][0], rm.synthetic((640,), 9, "bias"))
+    rules = (("batch", "data"), ("heads", "model"), ("hidden", "model"))
+    x_host = rm.synthetic((8, 256, 640), 5)
+    x = ljs.device_put(x_host, ljs.NamedSharding(mesh, ljs.PartitionSpec("data", "model")))
+    params = model.shard_params(host, mesh, rules)
+    want = rm.mha_sum_loss_grads(x_host, host, 8, 64, causal)
+    with mesh, ljs.nn.axis_rules(rules):
+        grads = ljs.train.attention_sum_loss_grads(model, params, x)
+        for name, g in grads.items():
+            scale = want[name].abs().max().item()
+            torch.testing.assert_close(g.global_array().cpu(), want[name], rtol=3e-2, atol=3e-2 * scale,
+                                       msg=lambda m, n=name: n + ": " + m)
+        state = ljs.train.attention_train_state(model, params, ljs.train.adam(learning_rate=0.001))
+        state = ljs.train.attention_train_step(model, state, x)
+        y = model(ljs.train.attention_params_of(state), x)                    # the updated parameters still run forward
+    assert state.step == 1 and y.shape == (8, 256, 640)
+    moved = (state.params["to_q"].global_array().cpu() - host["to_q"]).abs()
+    assert 0.5e-3 < moved.mean().item() <= 1.01e-3                            # first Adam step: |update| = lr almost everywhere
