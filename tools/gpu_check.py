@@ -389,6 +389,12 @@ def main():
                 torch.autograd.grad(ot, (qt, kt, vt), dot, retain_graph=True)
             ms2 = time_fn(sdpa_bwd, iters=5, warmup=2)
             print(f"    torch sdpa backward: {ms2:.3f} ms {fl / ms2 / 1e9:.1f} TFLOP/s", flush=True)
+    elif args.what == "attn_bwd_prof":
+        q, k, v, do = (torch.randn(2, 4096, 16, 128, device="cuda").to(torch.bfloat16) for _ in range(4))
+        o, lse = capi.attention_fwd_lse(q, k, v)
+        for _ in range(3):
+            capi.attention_bwd(q, k, v, o, do, lse)
+        torch.cuda.synchronize()
     elif args.what == "attn_quick":
         # one line per call, for A/B runs of library variants: burst (5 iterations) non-causal / causal and a sustained
         # run (300 launches) with the NVML clock, all at B8 S4096 H32 D128
