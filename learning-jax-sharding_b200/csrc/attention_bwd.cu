@@ -13,8 +13,9 @@
 // [query][key] in 128-byte-swizzled 64-key chunks: that one image is K-major for dS (dQ = dS K) and MN-major for its
 // transpose (dV = P^T dO, dK = dS^T Q).  Tensor memory: S | dP | dV | dK (4 x 128 columns); dQ reuses S's columns once the
 // compute warps have read S.  Shared memory (D = 128): K_j, V_j, Q_i, 2 x dO_i, P, dS = 7 x 32 KB.  dO is double-buffered so
-// that dP of the next step (which needs neither S's columns nor Q) runs under the dQ read-out and the Q load of that step
-// (DESIGN.md section 4.6 has the measured rates of this and of the single-buffered first version).
+// that dP of the next step (which needs neither S's columns nor Q) runs under the dQ read-out and the Q load of that step;
+// S, dP, P and dS each have their own barrier, so dV += P^T dO runs under the dS pass (DESIGN.md section 4.6 has the measured
+// rates of this and of the earlier versions).
 //
 //   warp 0   TMA producer: K_j, V_j once; dO_i one step ahead, Q_i per step
 //   warp 1   MMA issuer
@@ -75,11 +76,13 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
   uint64_t* kv_full = bars;          // TMA bytes of K_j and V_j
   uint64_t* q_full = bars + 1;       // TMA bytes of Q_i
   uint64_t* step_done = bars + 2;    // MMA commit after MMAs 3-5 of a step: sQ / sDO[.] / sP / sDS are free, dQ is in TMEM
-  uint64_t* sdp_full = bars + 3;     // MMA commit after MMAs 1-2: S and dP are in TMEM
-  uint64_t* pds_full = bars + 4;     // 8 warp arrivals: P and dS are in shared memory (S and dP have been read)
+  uint64_t* s_full = bars + 3;       // MMA commit: S is in TMEM
+  uint64_t* p_full = bars + 4;       // 8 warp arrivals: P is in shared memory (S has been read)
   uint64_t* dq_free = bars + 5;      // 8 warp arrivals: dQ has been read out of S's columns
   uint64_t* do_full = bars + 6;      // [2] TMA bytes of dO_i
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 8);
+  uint64_t* dp_full = bars + 8;      // MMA commit: dP is in TMEM
+  uint64_t* ds_full = bars + 9;      // 8 warp arrivals: dS is in shared memory (dP has been read)
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 10);
 
   const int warp = uniform_warp_idx();
   const int lane = threadIdx.x & 31;
@@ -101,8 +104,10 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     mbar_init(kv_full, 1);
     mbar_init(q_full, 1);
     mbar_init(step_done, 1);
-    mbar_init(sdp_full, 1);
-    mbar_init(pds_full, 8);
+    mbar_init(s_full, 1);
+    mbar_init(p_full, 8);
+    mbar_init(dp_full, 1);
+    mbar_init(ds_full, 8);
     mbar_init(dq_free, 8);
     mbar_init(&do_full[0], 1);
     mbar_init(&do_full[1], 1);
@@ -163,11 +168,11 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     const uint32_t t_s = tmem_base + Cfg::kSCol, t_dp = tmem_base + Cfg::kDPCol;
     const uint32_t t_dv = tmem_base + Cfg::kDVCol, t_dk = tmem_base + Cfg::kDKCol;
     mbar_wait(kv_full, 0);
-    for (int s = 0; s < nsteps; ++s) {
-      const uint64_t do_k = desc_advance(do_k0, (s & 1) * Cfg::kTileBytes);
-      const uint64_t do_mn = desc_advance(do_mn0, (s & 1) * Cfg::kTileBytes);
-      // dP first: it needs neither Q_i nor S's columns (which hold dQ of the previous step until it has been read out)
-      mbar_wait(&do_full[s & 1], (s >> 1) & 1);
+    // The tensor pipe never waits for a whole softmax pass: per step S -> [P pass] -> dV while [dS pass] -> dK, dQ -> dP of
+    // the NEXT step (it needs neither Q nor S's columns), so that dP is ready when the dS pass of that step wants it.
+    auto issue_dp = [&](int st) {
+      const uint64_t do_k = desc_advance(do_k0, (st & 1) * Cfg::kTileBytes);
+      mbar_wait(&do_full[st & 1], (st >> 1) & 1);
       tc_fence_after();
       if (elect_one()) {
 #pragma unroll
@@ -175,10 +180,15 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
           const uint32_t o = (kk >> 2) * (128 * 128) + (kk & 3) * 32;
           mma_bf16_ss(t_dp, desc_advance(do_k, o), desc_advance(v_k, o), idesc_s, kk > 0);
         }
+        mma_commit(dp_full);
       }
       __syncwarp();
+    };
+    issue_dp(0);
+    for (int s = 0; s < nsteps; ++s) {
+      const uint64_t do_mn = desc_advance(do_mn0, (s & 1) * Cfg::kTileBytes);
       mbar_wait(q_full, s & 1);
-      if (s > 0) mbar_wait(dq_free, (s - 1) & 1);
+      if (s > 0) mbar_wait(dq_free, (s - 1) & 1);       // S's columns hold dQ of the previous step until it has been read out
       tc_fence_after();
       if (elect_one()) {
 #pragma unroll
@@ -186,10 +196,10 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
           const uint32_t o = (kk >> 2) * (128 * 128) + (kk & 3) * 32;
           mma_bf16_ss(t_s, desc_advance(q_k, o), desc_advance(k_k, o), idesc_s, kk > 0);
         }
-        mma_commit(sdp_full);
+        mma_commit(s_full);
       }
       __syncwarp();
-      mbar_wait(pds_full, s & 1);
+      mbar_wait(p_full, s & 1);
       tc_fence_after();
       if (elect_one()) {
 #pragma unroll
@@ -197,6 +207,11 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
           const uint32_t o = kk * (16 * 128);
           mma_bf16_ss(t_dv, desc_advance(p_mn, o), desc_advance(do_mn, o), idesc_t, (s > 0 || kk > 0) ? 1u : 0u);
         }
+      }
+      __syncwarp();
+      mbar_wait(ds_full, s & 1);
+      tc_fence_after();
+      if (elect_one()) {
 #pragma unroll
         for (int kk = 0; kk < kBwBM / 16; ++kk) {
           const uint32_t o = kk * (16 * 128);
@@ -210,6 +225,7 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         mma_commit(step_done);
       }
       __syncwarp();
+      if (s + 1 < nsteps) issue_dp(s + 1);
     }
   } else if (warp >= 4) {
     // ===================== P, dS, dQ reduction, dK / dV epilogue =====================
@@ -226,32 +242,30 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       int limit = p.Sk - t0;                           // keys [0, limit) of this tile are visible to this row
       if (p.causal) limit = min(limit, f + off + 1 - t0);
       if (!row_valid) limit = 0;
-      mbar_wait(sdp_full, s & 1);
+      mbar_wait(s_full, s & 1);
       tc_fence_after();
       if (s > 0) {
         // sP / sDS doubled as the dQ staging tile of the previous step: the TMA reduce must have read it
         if (warp == 4 && lane == 0) tma_store_wait_read<0>();
         bwd_group_barrier();
       }
-#pragma unroll 1
-      for (int c = 2 * grp; c < 2 * grp + 2; ++c) {
-        uint32_t sv[32], dv[32];
+      // ---- P pass (this thread: its row, 64 keys), kept in registers for the dS pass
+      float pf[64];
+#pragma unroll
+      for (int cc = 0; cc < 2; ++cc) {
+        const int c = 2 * grp + cc;
+        uint32_t sv[32];
         tmem_ld_32x32(lane_base + Cfg::kSCol + c * 32, sv);
-        tmem_ld_32x32(lane_base + Cfg::kDPCol + c * 32, dv);
         tmem_wait_ld();
-        uint32_t pp[16], dd[16];
+        uint32_t pp[16];
 #pragma unroll
         for (int k = 0; k < 32; k += 2) {
-          float pv[2], dsv[2];
 #pragma unroll
           for (int e = 0; e < 2; ++e) {
             const int key = c * 32 + k + e;
-            const float pe = key < limit ? exp2_approx(__uint_as_float(sv[k + e]) * p.scale_log2 - lse) : 0.f;
-            pv[e] = pe;
-            dsv[e] = pe * (__uint_as_float(dv[k + e]) - dl) * p.scale;
+            pf[cc * 32 + k + e] = key < limit ? exp2_approx(__uint_as_float(sv[k + e]) * p.scale_log2 - lse) : 0.f;
           }
-          pp[k >> 1] = pack_bf16x2(pv[0], pv[1]);
-          dd[k >> 1] = pack_bf16x2(dsv[0], dsv[1]);
+          pp[k >> 1] = pack_bf16x2(pf[cc * 32 + k], pf[cc * 32 + k + 1]);
         }
         // row r, keys [32 c, 32 c + 32): four 16-byte units of the 128-byte-swizzled 64-key chunk
         const uint32_t row_off = (c >> 1) * (kBwBM * 128) + r * 128;
@@ -259,13 +273,39 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         for (int u = 0; u < 4; ++u) {
           const uint32_t unit = ((c & 1) * 4 + u) ^ (r & 7);
           *reinterpret_cast<uint4*>(sP + row_off + (unit << 4)) = make_uint4(pp[4 * u], pp[4 * u + 1], pp[4 * u + 2], pp[4 * u + 3]);
-          *reinterpret_cast<uint4*>(sDS + row_off + (unit << 4)) = make_uint4(dd[4 * u], dd[4 * u + 1], dd[4 * u + 2], dd[4 * u + 3]);
         }
       }
       fence_async_smem();                              // generic-proxy stores -> visible to the MMAs' async-proxy reads
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(pds_full);
+      if (lane == 0) mbar_arrive(p_full);              // dV += P^T dO may start
+      // ---- dS pass
+      mbar_wait(dp_full, s & 1);
+      tc_fence_after();
+#pragma unroll
+      for (int cc = 0; cc < 2; ++cc) {
+        const int c = 2 * grp + cc;
+        uint32_t dv[32];
+        tmem_ld_32x32(lane_base + Cfg::kDPCol + c * 32, dv);
+        tmem_wait_ld();
+        uint32_t dd[16];
+#pragma unroll
+        for (int k = 0; k < 32; k += 2) {
+          const float d0 = pf[cc * 32 + k] * (__uint_as_float(dv[k]) - dl) * p.scale;
+          const float d1 = pf[cc * 32 + k + 1] * (__uint_as_float(dv[k + 1]) - dl) * p.scale;
+          dd[k >> 1] = pack_bf16x2(d0, d1);
+        }
+        const uint32_t row_off = (c >> 1) * (kBwBM * 128) + r * 128;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const uint32_t unit = ((c & 1) * 4 + u) ^ (r & 7);
+          *reinterpret_cast<uint4*>(sDS + row_off + (unit << 4)) = make_uint4(dd[4 * u], dd[4 * u + 1], dd[4 * u + 2], dd[4 * u + 3]);
+        }
+      }
+      fence_async_smem();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(ds_full);             // dK += dS^T Q and dQ = dS K may start
       // ---- dQ_i of this step: TMEM (S's columns) -> f32 accumulator in global memory
       mbar_wait(step_done, s & 1);
       tc_fence_after();
