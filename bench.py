@@ -116,6 +116,47 @@ class ClockSampler:
                 "power_w_max": max((s[1] for s in self.samples), default=None), "samples": len(sm), "reasons": reasons}
 
 
+def train_kernel_sample(dev, peaks):
+    """CUDA-event timings of the backward-side kernels at the case5 shape (B8, S4096, 32 heads x 128, d_model 4096):
+    attention backward, the weight-gradient GEMM dW = x^T . dy, and the Adam update of one 4096 x 4096 kernel."""
+    import torch
+    from learning_jax_sharding_b200 import capi
+
+    def timed(fn, iters=5, warmup=2):
+        for _ in range(warmup):
+            fn()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        torch.cuda.synchronize(dev)
+        return e0.elapsed_time(e1) / iters
+
+    B, S, H, D, M = 8, 4096, 32, 128, 4096
+    q, k, v, do = (torch.randn(B, S, H, D, device=dev).to(torch.bfloat16) for _ in range(4))
+    o, lse = capi.attention_fwd_lse(q, k, v)
+    ms_bwd = timed(lambda: capi.attention_bwd(q, k, v, o, do, lse))
+    bwd_flops = 2.5 * 4.0 * B * H * S * S * D
+    del q, k, v, do, o, lse
+    x = torch.randn(B * S, M, device=dev).to(torch.bfloat16)
+    dy = torch.randn(B * S, M, device=dev).to(torch.bfloat16)
+    dw = torch.empty(M, M, device=dev, dtype=torch.float32)
+    ms_dw = timed(lambda: capi.gemm_bf16_tn(x, dy, out=dw))
+    n = M * M
+    p, mu, nu = (torch.randn(n, device=dev) for _ in range(3))
+    nu.abs_()
+    g = dw.reshape(-1)
+    ms_adam = timed(lambda: capi.adam_step(p, g, mu, nu, step=3), iters=20)
+    return {"workload": "case5 shape: attention backward (dQ, dK, dV; 2.5 x the forward's FLOPs), dW = x^T . dy "
+                        "(32768 x 4096 x 4096), Adam on 4096 x 4096 f32",
+            "attention_bwd_tflops": bwd_flops / (ms_bwd * 1e-3) / 1e12, "attention_bwd_ms": ms_bwd,
+            "dw_gemm_tflops": 2.0 * B * S * M * M / (ms_dw * 1e-3) / 1e12, "dw_gemm_ms": ms_dw,
+            "dw_gemm_frac_of_peak": 2.0 * B * S * M * M / (ms_dw * 1e-3) / 1e12 / peaks["bf16_burst"],
+            "adam_gbs": 28.0 * n / (ms_adam * 1e-3) / 1e9, "adam_ms": ms_adam,
+            "adam_frac_of_hbm_peak": 28.0 * n / (ms_adam * 1e-3) / 1e9 / peaks.get("hbm_gbs", 6551.4)}
+
+
 def ffn_flops(cfg):
     return 4.0 * cfg["batch"] * cfg["seq"] * cfg["d_model"] * cfg["d_ff"]
 
@@ -326,6 +367,11 @@ def main():
             "core_tflops": r["core_flops"] / (r["parts_ms"]["attn"] * 1e-3) / 1e12,
             "core_frac_of_peak": r["core_flops"] / (r["parts_ms"]["attn"] * 1e-3) / 1e12 / peaks["bf16_burst"],
             "parts_ms": r["parts_ms"], "gpu_launches": r["launches"]}
+        # supplementary: the kernels the reference's train_step adds at the same shape
+        try:
+            line["train_kernels"] = train_kernel_sample(dev, peaks)
+        except Exception as e:   # noqa: BLE001 - never lose the main line over the supplement
+            line["train_kernels"] = {"error": repr(e)}
     if not args.no_cpu_baseline and world == 1:
         line["cpu_baseline"] = cpu_ffn_sample(cfg, act=args.act)
     else:
