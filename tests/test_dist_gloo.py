@@ -61,6 +61,21 @@ def _worker(rank, world, port, results):
     z = ljs.reshard(ljs.device_put(t, ns(P(None, "model"))), ns(P(None, None, "model")))
     ok["all_to_all"] = torch.equal(z.device_buffers[0], t[:, :, 3 * rank:3 * rank + 3])
     ok["global"] = torch.equal(z.global_array(), t)
+    # (4) train_step over the data axis (one process per device): Dense module, then the attention module (heads layout)
+    xd, wd = rm.synthetic((4, 8, 32), 11), rm.synthetic((32, 16), 12, "weight")
+    st = ljs.train.TrainState.create(apply_fn=None, params={"kernel": ljs.device_put(wd.clone(), nf(P("data", None)))},
+                                     tx=ljs.train.adam(0.001))
+    st = ljs.train.dense_train_step(st, ljs.device_put(xd, nf(P("data"))))
+    k2, _, _, _ = rm.dense_train_step(xd, wd, torch.zeros_like(wd), torch.zeros_like(wd), 1)
+    ok["dense_train"] = torch.allclose(st.params["kernel"].device_buffers[0], k2[16 * rank:16 * rank + 16], rtol=0, atol=2e-5)
+    dp = ljs.Mesh(ljs.create_device_mesh((2, 1)), ("data", "model"))
+    with dp, ljs.nn.axis_rules(rules):
+        params = model.shard_params(host, dp, rules)
+        grads = ljs.train.attention_sum_loss_grads(model, params, ljs.device_put(xh, ljs.NamedSharding(dp, P("data", "model"))))
+    want_g = rm.mha_sum_loss_grads(xh, host, 4, 8)
+    ok["attn_grads"] = all(
+        torch.allclose(grads[n].device_buffers[0], want_g[n], rtol=3e-2, atol=3e-2 * want_g[n].abs().max().item())
+        for n in ("to_q", "to_k", "to_v", "to_out_0.kernel", "to_out_0.bias"))
     results[rank] = ok
     rt.barrier()
     torch.distributed.destroy_process_group()

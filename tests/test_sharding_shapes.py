@@ -121,3 +121,23 @@ def test_named_sharding_short_spec_and_replicated(ljs):
         ljs.NamedSharding(mesh, ljs.PartitionSpec("data", "data"))
     with pytest.raises(ValueError):
         s.shard_shape((7, 2))
+
+
+def test_visualize_array_sharding_text(ljs):
+    """jax.debug.visualize_array_sharding (case1a.py:26,32,51): one cell per distinct block, labelled with its devices."""
+    ljs.init_virtual(8, "cpu")
+    s = ljs.PositionalSharding(ljs.create_device_mesh((2, 4)))
+    import torch
+    a = ljs.device_put(torch.zeros(4, 16), s.replicate(axis=0, keepdims=True))        # case1a.py:24: columns over 4, replicated over 2
+    text = ljs.debug.sharding_text(a, platform="CPU")
+    cells = [c.strip() for c in text.splitlines()[1].strip("|").split("|")]
+    assert cells == ["CPU 0,4", "CPU 1,5", "CPU 2,6", "CPU 3,7"]
+    b = ljs.device_put(torch.zeros(16, 4), s.reshape(4, 2).replicate(axis=1, keepdims=True))   # case1a.py:30
+    rows = [ln for ln in ljs.debug.sharding_text(b, platform="CPU").splitlines() if ln.startswith("|")]
+    assert [r.strip("|").strip() for r in rows] == ["CPU 0,1", "CPU 2,3", "CPU 4,5", "CPU 6,7"]
+    mesh = ljs.Mesh(ljs.create_device_mesh((2, 4)), ("data", "model"))
+    v = ljs.device_put(torch.zeros(8), ljs.NamedSharding(mesh, ljs.PartitionSpec("data")))
+    assert "CPU 0,1,2,3" in ljs.debug.sharding_text(v, platform="CPU")
+    import pytest
+    with pytest.raises(ValueError):
+        ljs.debug.sharding_text(ljs.device_put(torch.zeros(2, 2, 2), ljs.NamedSharding(mesh, ljs.PartitionSpec())))
