@@ -30,6 +30,10 @@
 
 namespace b200 {
 
+#ifndef B200_ATTN_PROFILE
+#define B200_ATTN_PROFILE 0   // 1: per-phase clock64 totals of block (0,0,0) into AttnBwdParams::prof (tools/gpu_check.py attn_bwd_phases)
+#endif
+
 constexpr int kBwBM = 128;      // query rows per step
 constexpr int kBwBN = 128;      // keys per CTA
 constexpr int kBwThreads = 384;
@@ -52,6 +56,7 @@ struct AttnBwdParams {
   float scale, scale_log2;
   int causal;
   int num_q_tiles;
+  long long* prof;        // bring-up aid: compute warp 4 -> [0..7], MMA warp -> [8..15]
 };
 
 __device__ __forceinline__ void bwd_group_barrier() {      // the 256 compute threads (warps 4..11)
@@ -184,12 +189,23 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       }
       __syncwarp();
     };
+    const bool mprof = B200_ATTN_PROFILE && p.prof != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0;
+    long long macc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    long long mtp = mprof ? clock64() : 0;
+#if B200_ATTN_PROFILE
+#define MMARK(k) do { if (mprof) { long long _t = clock64(); macc[k] += _t - mtp; mtp = _t; } } while (0)
+#else
+#define MMARK(k) do { } while (0)
+#endif
     issue_dp(0);
+    MMARK(6);
     for (int s = 0; s < nsteps; ++s) {
       const uint64_t do_mn = desc_advance(do_mn0, (s & 1) * Cfg::kTileBytes);
       mbar_wait(q_full, s & 1);
+      MMARK(0);
       if (s > 0) mbar_wait(dq_free, (s - 1) & 1);       // S's columns hold dQ of the previous step until it has been read out
       tc_fence_after();
+      MMARK(1);
       if (elect_one()) {
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk) {
@@ -199,8 +215,10 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         mma_commit(s_full);
       }
       __syncwarp();
+      MMARK(2);
       mbar_wait(p_full, s & 1);
       tc_fence_after();
+      MMARK(3);
       if (elect_one()) {
 #pragma unroll
         for (int kk = 0; kk < kBwBM / 16; ++kk) {       // contraction over the 128 query rows: 16 rows = 2 KB per step
@@ -209,8 +227,10 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         }
       }
       __syncwarp();
+      MMARK(2);
       mbar_wait(ds_full, s & 1);
       tc_fence_after();
+      MMARK(4);
       if (elect_one()) {
 #pragma unroll
         for (int kk = 0; kk < kBwBM / 16; ++kk) {
@@ -225,7 +245,13 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         mma_commit(step_done);
       }
       __syncwarp();
+      MMARK(2);
       if (s + 1 < nsteps) issue_dp(s + 1);
+      MMARK(5);
+    }
+    if (mprof) {
+      for (int k = 0; k < 7; ++k) p.prof[8 + k] = macc[k];
+      p.prof[15] = nsteps;
     }
   } else if (warp >= 4) {
     // ===================== P, dS, dQ reduction, dK / dV epilogue =====================
@@ -234,6 +260,14 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     const int r = quad * 32 + lane;                    // query row of the step's tile (and key row in the epilogue)
     const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
     const int64_t bh = static_cast<int64_t>(batch) * p.H + head;
+    const bool cprof = B200_ATTN_PROFILE && p.prof != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && warp == 4 && lane == 0;
+    long long cacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    long long ctp = cprof ? clock64() : 0;
+#if B200_ATTN_PROFILE
+#define CMARK(k) do { if (cprof) { long long _t = clock64(); cacc[k] += _t - ctp; ctp = _t; } } while (0)
+#else
+#define CMARK(k) do { } while (0)
+#endif
     for (int s = 0; s < nsteps; ++s) {
       const int f = (i_start + s) * kBwBM + r;
       const bool row_valid = f < p.Sq;
@@ -244,11 +278,15 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       if (!row_valid) limit = 0;
       mbar_wait(s_full, s & 1);
       tc_fence_after();
+      CMARK(0);
       if (s > 0) {
-        // sP / sDS doubled as the dQ staging tile of the previous step: the TMA reduce must have read it
-        if (warp == 4 && lane == 0) tma_store_wait_read<0>();
+        // sP / sDS doubled as the dQ staging tile of the previous step, handed to TMA as D/32 bulk groups in column order:
+        // sP is free once all but the last D/64 groups have been read (the reduce runs at ~34 B/clk per SM, so waiting for
+        // the whole tile here cost ~1900 cycles per step); sDS is waited for before the dS pass
+        if (warp == 4 && lane == 0) tma_store_wait_read<D / 64>();
         bwd_group_barrier();
       }
+      CMARK(1);
       // ---- P pass (this thread: its row, 64 keys), kept in registers for the dS pass
       float pf[64];
 #pragma unroll
@@ -279,9 +317,15 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(p_full);              // dV += P^T dO may start
+      CMARK(2);
       // ---- dS pass
       mbar_wait(dp_full, s & 1);
       tc_fence_after();
+      if (s > 0) {
+        if (warp == 4 && lane == 0) tma_store_wait_read<0>();
+        bwd_group_barrier();
+      }
+      CMARK(3);
 #pragma unroll
       for (int cc = 0; cc < 2; ++cc) {
         const int c = 2 * grp + cc;
@@ -306,9 +350,11 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(ds_full);             // dK += dS^T Q and dQ = dS K may start
+      CMARK(4);
       // ---- dQ_i of this step: TMEM (S's columns) -> f32 accumulator in global memory
       mbar_wait(step_done, s & 1);
       tc_fence_after();
+      CMARK(5);
       // this thread's D/2 columns of its row -> the staging tile (f32, [32-column chunk][row][128 B], 16-byte units XOR-swizzled
       // like the tensor map), then ONE thread hands the tile to TMA: dq_acc[b, f0.., head, :] += tile, rows past Sq clipped
 #pragma unroll 1
@@ -321,6 +367,7 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         for (int u = 0; u < 8; ++u)
           *reinterpret_cast<uint4*>(dst + ((u ^ (r & 7)) << 4)) = make_uint4(q[4 * u], q[4 * u + 1], q[4 * u + 2], q[4 * u + 3]);
       }
+      // (arriving on dq_free before these stores -- all columns loaded first -- was measured and is slower: 730 vs 774 TFLOP/s)
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(dq_free);             // S's columns may take the next step's scores
@@ -328,10 +375,15 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       bwd_group_barrier();
       if (warp == 4 && lane == 0) {
 #pragma unroll
-        for (int c = 0; c < D / 32; ++c)
+        for (int c = 0; c < D / 32; ++c) {
           tma_reduce_add_4d(&tmDQ, sP + c * (kBwBM * 128), c * 32, head, (i_start + s) * kBwBM, batch);
-        tma_store_commit();
+          tma_store_commit();                          // one bulk group per 32-column chunk, in buffer order
+        }
       }
+      CMARK(6);
+    }
+    if (cprof) {
+      for (int k = 0; k < 7; ++k) p.prof[k] = cacc[k];
     }
     if (warp == 4 && lane == 0) tma_store_wait_all<0>();  // the last tile has left shared memory (and landed) before the CTA exits
     // ---- dK_j, dV_j: complete after the last step's MMAs (step_done of the last step has been waited for above)
@@ -450,6 +502,7 @@ static int launch_attention_bwd(const void* Q, const void* K, const void* V, con
 }  // namespace b200
 
 using namespace b200;
+namespace b200 { extern long long* g_attn_prof; }
 
 extern "C" int b200_attention_bwd(const b200_attention_bwd_args* a, void* stream) {
   B200_REQUIRE(a, "b200_attention_bwd: null args");
@@ -494,6 +547,7 @@ extern "C" int b200_attention_bwd(const b200_attention_bwd_args* a, void* stream
   p.scale_log2 = a->scale * 1.4426950408889634f;
   p.causal = a->causal ? 1 : 0;
   p.num_q_tiles = (Sq + kBwBM - 1) / kBwBM;
+  p.prof = g_attn_prof;
   int rc = D == 64 ? launch_attention_bwd<64>(a->Q, a->K, a->V, a->O, a->dO, p, delta, B, Sq, Sk, H, a->strides, st)
                    : launch_attention_bwd<128>(a->Q, a->K, a->V, a->O, a->dO, p, delta, B, Sq, Sk, H, a->strides, st);
   if (rc != B200_OK) return rc;

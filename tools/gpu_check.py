@@ -395,6 +395,31 @@ def main():
         for _ in range(3):
             capi.attention_bwd(q, k, v, o, do, lse)
         torch.cuda.synchronize()
+    elif args.what == "attn_bwd_phases":
+        # needs a build with B200_EXTRA_NVCC_FLAGS=-DB200_ATTN_PROFILE=1
+        import ctypes
+        lib = capi.load()
+        lib.b200_attention_set_profile_buffer.argtypes = [ctypes.c_void_p]
+        buf = torch.zeros(16, dtype=torch.int64, device="cuda")
+        B, S, H, D = 8, 4096, 32, 128
+        q, k, v, do = (torch.randn(B, S, H, D, device="cuda").to(torch.bfloat16) for _ in range(4))
+        o, lse = capi.attention_fwd_lse(q, k, v)
+        for _ in range(2):
+            capi.attention_bwd(q, k, v, o, do, lse)
+        lib.b200_attention_set_profile_buffer(ctypes.c_void_p(buf.data_ptr()))
+        capi.attention_bwd(q, k, v, o, do, lse)
+        torch.cuda.synchronize()
+        lib.b200_attention_set_profile_buffer(None)
+        t = buf.cpu().tolist()
+        n = max(t[15], 1)
+        print(f"  attention backward, block (0,0,0), {n} steps, cycles per step:")
+        for name, c in zip(["wait S", "wait staging read + barrier", "P pass + arrive", "wait dP", "dS pass + arrive",
+                            "wait step_done (dV, dK, dQ MMAs)", "dQ read-out + staging + TMA issue"], t[:7]):
+            print(f"    compute warp 4: {name:38s} {c / n:8.0f}")
+        print(f"    {'compute total':54s} {sum(t[:7]) / n:8.0f}")
+        for name, c in zip(["wait Q", "wait dq_free", "issue calls (S, dV, dK+dQ)", "wait P", "wait dS", "issue dP of next step (incl. wait dO)",
+                            "first dP"], t[8:15]):
+            print(f"    MMA warp: {name:44s} {c / n:8.0f}")
     elif args.what == "attn_quick":
         # one line per call, for A/B runs of library variants: burst (5 iterations) non-causal / causal and a sustained
         # run (300 launches) with the NVML clock, all at B8 S4096 H32 D128
