@@ -8,8 +8,6 @@ timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 2>/dev/null | grep '^{' | cut -c1-400 >> $L
 timeout 600 python bench.py > gpurun_out/bench_r01_final2.json 2>gpurun_out/bench_r01_final2.err; echo "bench exit=$?" >> $L
 cut -c1-2600 gpurun_out/bench_r01_final2.json >> $L
-CMD="python tools/gpu_check.py attn_bwd_prof"
-timeout 300 $CMD > gpurun_out/plain_bwd.log 2>&1 && \
-timeout 1200 ncu --set full --clock-control none --import-source on -k regex:attention_bwd -s 1 -c 1 -o gpurun_out/prof_attn_bwd $CMD > gpurun_out/ncu_attn_bwd.log 2>&1
-echo "ncu bwd exit=$?" >> $L
+CMD="python tools/gpu_check.py attn_bwd_time"
+timeout 300 $CMD > gpurun_out/plain_bwd.log 2>&1; echo "bwd_time exit=$?" >> $L; grep "attn bwd" gpurun_out/plain_bwd.log >> $L
 cat $L
