@@ -276,6 +276,8 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       int limit = p.Sk - t0;                           // keys [0, limit) of this tile are visible to this row
       if (p.causal) limit = min(limit, f + off + 1 - t0);
       if (!row_valid) limit = 0;
+      const bool all_visible = __all_sync(0xffffffffu, limit >= kBwBN);   // warp-uniform: interior tiles skip the per-key select
+      const float neg_lse = -lse, dls = dl * p.scale;
       mbar_wait(s_full, s & 1);
       tc_fence_after();
       CMARK(0);
@@ -301,7 +303,8 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
 #pragma unroll
           for (int e = 0; e < 2; ++e) {
             const int key = c * 32 + k + e;
-            pf[cc * 32 + k + e] = key < limit ? exp2_approx(__uint_as_float(sv[k + e]) * p.scale_log2 - lse) : 0.f;
+            const float pe = exp2_approx(fmaf(__uint_as_float(sv[k + e]), p.scale_log2, neg_lse));
+            pf[cc * 32 + k + e] = (all_visible || key < limit) ? pe : 0.f;
           }
           pp[k >> 1] = pack_bf16x2(pf[cc * 32 + k], pf[cc * 32 + k + 1]);
         }
@@ -335,8 +338,8 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         uint32_t dd[16];
 #pragma unroll
         for (int k = 0; k < 32; k += 2) {
-          const float d0 = pf[cc * 32 + k] * (__uint_as_float(dv[k]) - dl) * p.scale;
-          const float d1 = pf[cc * 32 + k + 1] * (__uint_as_float(dv[k + 1]) - dl) * p.scale;
+          const float d0 = pf[cc * 32 + k] * fmaf(__uint_as_float(dv[k]), p.scale, -dls);       // p * scale * (dP - delta)
+          const float d1 = pf[cc * 32 + k + 1] * fmaf(__uint_as_float(dv[k + 1]), p.scale, -dls);
           dd[k >> 1] = pack_bf16x2(d0, d1);
         }
         const uint32_t row_off = (c >> 1) * (kBwBM * 128) + r * 128;
