@@ -420,6 +420,16 @@ def main():
         for name, c in zip(["wait Q", "wait dq_free", "issue calls (S, dV, dK+dQ)", "wait P", "wait dS", "issue dP of next step (incl. wait dO)",
                             "first dP"], t[8:15]):
             print(f"    MMA warp: {name:44s} {c / n:8.0f}")
+    elif args.what == "attn_bwd_var":
+        # run-to-run spread of the causal backward inside ONE process (the figure differed between boxes): 8 x 5 launches
+        B, S, H, D = 8, 4096, 32, 128
+        q, k, v, do = (torch.randn(B, S, H, D, device="cuda").to(torch.bfloat16) for _ in range(4))
+        for causal in (True, False):
+            o, lse = capi.attention_fwd_lse(q, k, v, causal=causal)
+            fl = 2.5 * ((2.0 * B * H * S * (S + 1) * D) if causal else 4.0 * B * H * S * S * D)
+            vals = [fl / time_fn(lambda: capi.attention_bwd(q, k, v, o, do, lse, causal=causal), iters=5, warmup=1) / 1e9
+                    for _ in range(8)]
+            print(f"  attn bwd causal={causal}: " + " ".join(f"{x:.0f}" for x in vals) + " TFLOP/s", flush=True)
     elif args.what == "attn_quick":
         # one line per call, for A/B runs of library variants: burst (5 iterations) non-causal / causal and a sustained
         # run (300 launches) with the NVML clock, all at B8 S4096 H32 D128
