@@ -491,9 +491,9 @@ class FFNBench:
             shard = (w1[rank * kl1:(rank + 1) * kl1].contiguous().to(dev), b1.to(dev),
                      w2[rank * kl2:(rank + 1) * kl2].contiguous().to(dev), b2.to(dev))
             self.layer = None
-            # measured (profiles/r01_fsdp_gather_modes.md): copy-engine pulls win at 2 GPUs (2293 vs NCCL 2171
-            # TFLOP/s), NCCL all-gather wins at 8 (4182 vs 3615); the one-kernel SM pull is behind both
-            default_mode = "peer" if world <= 2 else "nccl"
+            # measured with the forward prefetch (profiles/r01_fsdp_gather_modes.md): copy-engine pulls win at 2 GPUs (2706 vs
+            # NCCL 2501 TFLOP/s) and at 4 (5152 vs 4496), NCCL all-gather wins at 8 (7094 vs 6660); the SM pull is behind both
+            default_mode = "peer" if world <= 4 else "nccl"
             fsdp_mode = os.environ.get("B200_FSDP_COLLECTIVE", default_mode)
             prefetch = os.environ.get("B200_FSDP_PREFETCH", "1") != "0"
             # with the next call's W1 prefetched, each weight has a whole GEMM to arrive under: one chunk keeps the GEMMs at
