@@ -105,8 +105,22 @@ int b200_gemm_bf16_rowblocked(const void* A, int64_t lda, int a_rows_per_block, 
  * IPC (b200_peer_*), so partial sums cross NVLink straight out of the GEMM epilogue, tile by
  * tile, in 128-byte row segments.  m_block_rot staggers the ranks (rank r starts with block r+1)
  * so that no two ranks push to the same destination at once.  c_block_ptrs = NULL keeps the
- * result in C (rotation only).
+ * result in C (rotation only).  The scatter may be combined with the row-blocked A view when
+ * a_rows_per_block == m_rows_per_block: block b of the product is then read from rows
+ * [b * a_block_stride, b * a_block_stride + R) of A -- a token CHUNK of every owner's row block, so
+ * that the reduction of chunk c can run beside the GEMM of chunk c+1.
  */
+/* Launch-heuristic overrides carried by the call itself (the library keeps no tuning state between calls, so two host
+ * threads or two devices can never see each other's settings).  Zero in every field = the library's own choice. */
+typedef struct {
+  int cta_group;    /* 1 = one CTA per tile, 2 = CTA pairs (tcgen05 cta_group::2, 256-row tiles) */
+  int block_n;      /* 64, 128 or 256 columns per tile */
+  int group_m;      /* raster group: row-blocks that sweep all column-blocks together (L2 reuse of the A panels) */
+  int max_stages;   /* cap on the shared-memory ring depth */
+  int max_ctas;     /* cap on the persistent grid, e.g. to leave SMs to a collective kernel running beside the GEMM */
+  int k_serpentine; /* 1 = every other tile of a CTA walks K downwards */
+} b200_gemm_tuning;
+
 typedef struct {
   const void* A;
   int64_t lda;
@@ -124,6 +138,7 @@ typedef struct {
   int a_layout;                         /* B200_A_MK (0): A is [M,K] row-major; B200_A_KM: A is stored [K,M] row-major,
                                            i.e. the product is (stored A)^T . B -- the weight-gradient GEMM dW = x^T . dy of
                                            jax.grad through nn.Dense (case5_attention_dense.py:130-139) */
+  b200_gemm_tuning tune;                /* per-call overrides of the launch heuristics; all zero = library choice */
 } b200_gemm_args;
 int b200_gemm_bf16_ex(const b200_gemm_args* args, void* stream);
 
@@ -156,6 +171,24 @@ int b200_attention_fwd(const void* Q, const void* K, const void* V, void* O, int
                        int64_t k_stride_s, int64_t k_stride_h, int64_t v_stride_b, int64_t v_stride_s,
                        int64_t v_stride_h, int64_t o_stride_b, int64_t o_stride_s, int64_t o_stride_h, float scale,
                        int causal, void* stream);
+
+/*
+ * General form of b200_attention_fwd (zero-initialise, fill what you need): strides[12] = (batch, seq, head) element
+ * strides of Q, K, V, O in that order; lse2 (optional, f32 [B, H, Sq]) as in b200_attention_fwd_lse; variant picks the
+ * kernel for this call only -- 0 = library choice, 1 = one query tile per CTA (no lse2), 8 = persistent single-CTA
+ * kernel, 9 = persistent CTA-pair kernel (D = 128).  The library keeps no variant setting between calls.
+ */
+typedef struct {
+  const void *Q, *K, *V;
+  void* O;
+  float* lse2;
+  int B, Sq, Sk, H, D;
+  int64_t strides[12];
+  float scale;
+  int causal;
+  int variant;
+} b200_attention_args;
+int b200_attention_fwd_ex(const b200_attention_args* args, void* stream);
 
 /*
  * b200_attention_fwd that also returns lse2[B, H, Sq] (f32) = log2(sum_t exp2(log2(e) * scale * s[t])) per query row: the

@@ -33,7 +33,9 @@ EXPORTED_SYMBOLS = (
     "b200_gemm_bf16_ex",
     "b200_gemm_f32",
     "b200_attention_fwd",
+    "b200_attention_fwd_ex",
     "b200_ffn_fwd",
+    "b200_ffn_fwd_static_scratch",
     "b200_cast_f32_to_bf16",
     "b200_cast_bf16_to_f32",
     "b200_sum_partials_to_bf16",
@@ -63,6 +65,20 @@ EXPORTED_SYMBOLS = (
 )
 
 
+class GemmTuning(ctypes.Structure):
+    """b200_gemm_tuning of include/b200_sharded.h: per-call overrides of the launch heuristics (all zero = library choice)."""
+    _fields_ = [("cta_group", ctypes.c_int), ("block_n", ctypes.c_int), ("group_m", ctypes.c_int),
+                ("max_stages", ctypes.c_int), ("max_ctas", ctypes.c_int), ("k_serpentine", ctypes.c_int)]
+
+
+class AttentionArgs(ctypes.Structure):
+    """b200_attention_args of include/b200_sharded.h."""
+    _fields_ = [("Q", ctypes.c_void_p), ("K", ctypes.c_void_p), ("V", ctypes.c_void_p), ("O", ctypes.c_void_p),
+                ("lse2", ctypes.c_void_p), ("B", ctypes.c_int), ("Sq", ctypes.c_int), ("Sk", ctypes.c_int),
+                ("H", ctypes.c_int), ("D", ctypes.c_int), ("strides", ctypes.c_int64 * 12), ("scale", ctypes.c_float),
+                ("causal", ctypes.c_int), ("variant", ctypes.c_int)]
+
+
 class GemmArgs(ctypes.Structure):
     """b200_gemm_args of include/b200_sharded.h."""
     _fields_ = [("A", ctypes.c_void_p), ("lda", ctypes.c_int64), ("a_rows_per_block", ctypes.c_int),
@@ -70,7 +86,7 @@ class GemmArgs(ctypes.Structure):
                 ("b_layout", ctypes.c_int), ("bias", ctypes.c_void_p), ("C", ctypes.c_void_p), ("ldc", ctypes.c_int64),
                 ("out_dtype", ctypes.c_int), ("c_block_ptrs", ctypes.c_void_p), ("m_rows_per_block", ctypes.c_int),
                 ("m_block_rot", ctypes.c_int), ("M", ctypes.c_int), ("N", ctypes.c_int), ("K", ctypes.c_int),
-                ("epilogue", ctypes.c_int), ("a_layout", ctypes.c_int)]
+                ("epilogue", ctypes.c_int), ("a_layout", ctypes.c_int), ("tune", GemmTuning)]
 
 
 class AttentionBwdArgs(ctypes.Structure):
@@ -117,17 +133,14 @@ def load():
     lib.b200_sum_bf16_partials.argtypes = [vp, i64, i32, vp, i64, vp, i64, vp]
     lib.b200_gemm_f32.argtypes = [vp, i64, i64, vp, i64, i64, vp, i64, i64, i32, i32, i32, i32, i32, vp]
     lib.b200_attention_fwd.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32] + [i64] * 12 + [f32, i32, vp]
+    lib.b200_attention_fwd_ex.argtypes = [ctypes.POINTER(AttentionArgs), vp]
+    lib.b200_ffn_fwd_static_scratch.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp]
     lib.b200_attention_fwd_lse.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32] + [i64] * 12 + [f32, i32, vp]
     lib.b200_attention_bwd.argtypes = [ctypes.POINTER(AttentionBwdArgs), vp]
     lib.b200_ffn_fwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp]
     lib.b200_cast_f32_to_bf16.argtypes = [vp, vp, i64, vp]
     lib.b200_cast_bf16_to_f32.argtypes = [vp, vp, i64, vp]
     lib.b200_sum_partials_to_bf16.argtypes = [vp, i64, i32, vp, i64, vp, i64, vp]
-    lib.b200_gemm_set_tuning.argtypes = [i32, i32]
-    lib.b200_attention_set_variant.argtypes = [i32]
-    lib.b200_gemm_set_group_m.argtypes = [i32]
-    lib.b200_gemm_set_k_serpentine.argtypes = [i32]
-    lib.b200_gemm_set_max_ctas.argtypes = [i32]
     lib.b200_adam_step.argtypes = [vp, vp, i32, vp, vp, i64, f32, f32, f32, f32, i32, vp]
     lib.b200_comm_unique_id.argtypes = [vp]
     lib.b200_mesh_create.argtypes = [vp, i32, i32, ctypes.POINTER(i32), i32, ctypes.POINTER(vp)]
@@ -139,8 +152,7 @@ def load():
     lib.b200_ffn_fwd_tp.argtypes = [vp] * 9 + [i32] * 6 + [vp]
     for _n in ("b200_all_reduce", "b200_reduce_scatter", "b200_all_gather", "b200_all_to_all"):
         getattr(lib, _n).argtypes = [vp, vp, vp, i64, i32, vp]
-    for name in EXPORTED_SYMBOLS[3:] + ("b200_gemm_set_tuning", "b200_attention_set_variant", "b200_gemm_set_group_m",
-                                        "b200_gemm_set_k_serpentine", "b200_gemm_set_max_ctas"):
+    for name in EXPORTED_SYMBOLS[3:]:
         getattr(lib, name).restype = i32
     _lib = lib
     return lib
@@ -173,34 +185,19 @@ def launch_count() -> int:
     return int(load().b200_launch_count())
 
 
-def set_gemm_tuning(cta_group: int = 0, block_n: int = 0):
-    """Force the GEMM tile configuration (0 = library heuristic). For tests and tuning runs."""
-    _check(load().b200_gemm_set_tuning(cta_group, block_n), "b200_gemm_set_tuning")
-
-
-def set_gemm_group_m(group_m: int = 0):
-    """Tile rasterisation group size (row-blocks that sweep the columns together). Tuning hook."""
-    _check(load().b200_gemm_set_group_m(group_m), "b200_gemm_set_group_m")
-
-
-def set_gemm_max_ctas(ctas: int = 0):
-    """Upper bound on the persistent GEMM's grid (0 = one CTA per SM): leaves SMs to a collective kernel that runs
-    beside it.  Tuning hook."""
-    _check(load().b200_gemm_set_max_ctas(ctas), "b200_gemm_set_max_ctas")
-
-
-def set_gemm_k_serpentine(mode: int = -1):
-    """-1 = library heuristic, 0 / 1 = every other tile of a CTA walks K downwards off / on. Tuning hook."""
-    _check(load().b200_gemm_set_k_serpentine(mode), "b200_gemm_set_k_serpentine")
-
-
-def set_attention_variant(variant: int = 0):
-    """0 = library heuristic, 1 = one 128-row query tile per CTA, 2 = two tiles per CTA (ping-pong)."""
-    _check(load().b200_attention_set_variant(variant), "b200_attention_set_variant")
+def _tuning(tune) -> GemmTuning:
+    """``tune``: None or a dict with any of cta_group, block_n, group_m, max_stages, max_ctas, k_serpentine (see
+    b200_gemm_tuning).  The overrides travel with the call; the library keeps no tuning state."""
+    t = GemmTuning()
+    for k, v in (tune or {}).items():
+        if not hasattr(t, k):
+            raise B200Error(f"unknown GEMM tuning field {k!r}")
+        setattr(t, k, int(v))
+    return t
 
 
 def gemm_bf16(a, b, *, b_layout=B_KN, bias=None, epilogue=EPI_NONE, out=None, out_dtype=torch.bfloat16,
-              a_row_blocks=None):
+              a_row_blocks=None, tune=None):
     """out[M,N] = epilogue(a[M,K] @ B + bias). ``b`` is [K,N] (B_KN, a Dense kernel) or [N,K] (B_NK).
 
     a, b, out may be row-strided views (last dim contiguous).  ``a_row_blocks=(M, rows_per_block,
@@ -227,15 +224,21 @@ def gemm_bf16(a, b, *, b_layout=B_KN, bias=None, epilogue=EPI_NONE, out=None, ou
         raise B200Error("gemm_bf16: bad output tensor")
     if bias is not None and (bias.dtype != torch.bfloat16 or bias.numel() != N or not bias.is_contiguous()):
         raise B200Error("gemm_bf16: bias must be a contiguous bf16 vector of length N")
+    args = GemmArgs()
+    args.A, args.lda, args.a_rows_per_block, args.a_block_stride = a.data_ptr(), a.stride(0), rpb, bstride
+    args.B, args.ldb, args.b_layout = b.data_ptr(), b.stride(0), b_layout
+    args.bias = None if bias is None else bias.data_ptr()
+    args.C, args.ldc = out.data_ptr(), out.stride(0)
+    args.out_dtype = F32 if out.dtype == torch.float32 else BF16
+    args.M, args.N, args.K, args.epilogue = M, N, K, epilogue
+    args.tune = _tuning(tune)
     with torch.cuda.device(a.device):
-        rc = load().b200_gemm_bf16_rowblocked(
-            _ptr(a), a.stride(0), rpb, bstride, _ptr(b), b.stride(0), b_layout, _ptr(bias), _ptr(out), out.stride(0),
-            F32 if out.dtype == torch.float32 else BF16, M, N, K, epilogue, _stream(a))
+        rc = load().b200_gemm_bf16_ex(ctypes.byref(args), _stream(a))
     _check(rc, "b200_gemm_bf16")
     return out
 
 
-def gemm_bf16_tn(a_km, b, *, out=None, out_dtype=torch.bfloat16):
+def gemm_bf16_tn(a_km, b, *, out=None, out_dtype=torch.bfloat16, tune=None):
     """out[M,N] = a_km^T @ b with a_km stored [K,M] and b [K,N], both row-major bf16: the weight-gradient product
     dW = x^T @ dy of a Dense layer (b200_gemm_bf16_ex with a_layout = B200_A_KM; no transposed copy is made, the TMA
     loads MN-major tiles)."""
@@ -256,6 +259,7 @@ def gemm_bf16_tn(a_km, b, *, out=None, out_dtype=torch.bfloat16):
     args.C, args.ldc = out.data_ptr(), out.stride(0)
     args.out_dtype = F32 if out.dtype == torch.float32 else BF16
     args.M, args.N, args.K, args.epilogue = M, N, K, EPI_NONE
+    args.tune = _tuning(tune)
     with torch.cuda.device(b.device):
         rc = load().b200_gemm_bf16_ex(ctypes.byref(args), _stream(b))
     _check(rc, "b200_gemm_bf16_ex")
@@ -311,9 +315,11 @@ def gemm_f32(a, b, *, out=None, accumulate=False):
     return out
 
 
-def attention_fwd(q, k, v, *, scale=None, causal=False, out=None):
-    """softmax(scale * q k^T [+causal]) v with q [B,Sq,H,D], k/v [B,Sk,H,D] bf16 (b s n h layout)."""
-    _require_cuda(q, k, v, out)
+def attention_fwd(q, k, v, *, scale=None, causal=False, out=None, lse=None, variant=0):
+    """softmax(scale * q k^T [+causal]) v with q [B,Sq,H,D], k/v [B,Sk,H,D] bf16 (b s n h layout).  ``lse`` (optional
+    f32 [B,H,Sq]) receives log2 of the softmax denominator; ``variant`` forces a kernel for this call (0 = library
+    choice, 1 / 8 / 9 -- see b200_attention_args)."""
+    _require_cuda(q, k, v, out, lse)
     for t in (q, k, v):
         if t.dtype != torch.bfloat16 or t.dim() != 4 or t.stride(3) != 1:
             raise B200Error("attention_fwd takes 4-D bf16 tensors [B,S,H,D] with contiguous D")
@@ -323,34 +329,32 @@ def attention_fwd(q, k, v, *, scale=None, causal=False, out=None):
         raise B200Error(f"attention_fwd: shape mismatch q{tuple(q.shape)} k{tuple(k.shape)} v{tuple(v.shape)}")
     if out is None:
         out = torch.empty((B, Sq, H, D), dtype=torch.bfloat16, device=q.device)
-    if scale is None:
-        scale = D ** -0.5
+    if out.shape != (B, Sq, H, D) or out.dtype != torch.bfloat16 or out.stride(3) != 1:
+        raise B200Error("attention_fwd: bad output tensor")
+    if lse is not None and (lse.shape != (B, H, Sq) or lse.dtype != torch.float32 or not lse.is_contiguous()):
+        raise B200Error("attention_fwd: lse must be a contiguous f32 [B,H,Sq] tensor")
+    a = AttentionArgs()
+    a.Q, a.K, a.V, a.O = q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr()
+    a.lse2 = None if lse is None else lse.data_ptr()
+    a.B, a.Sq, a.Sk, a.H, a.D = B, Sq, Sk, H, D
+    st = []
+    for t in (q, k, v, out):
+        st += [t.stride(0), t.stride(1), t.stride(2)]
+    a.strides = (ctypes.c_int64 * 12)(*st)
+    a.scale = float(D ** -0.5 if scale is None else scale)
+    a.causal, a.variant = int(bool(causal)), int(variant)
     with torch.cuda.device(q.device):
-        rc = load().b200_attention_fwd(
-            _ptr(q), _ptr(k), _ptr(v), _ptr(out), B, Sq, Sk, H, D,
-            q.stride(0), q.stride(1), q.stride(2), k.stride(0), k.stride(1), k.stride(2),
-            v.stride(0), v.stride(1), v.stride(2), out.stride(0), out.stride(1), out.stride(2),
-            float(scale), int(bool(causal)), _stream(q))
+        rc = load().b200_attention_fwd_ex(ctypes.byref(a), _stream(q))
     _check(rc, "b200_attention_fwd")
     return out
 
 
-def attention_fwd_lse(q, k, v, *, scale=None, causal=False):
+def attention_fwd_lse(q, k, v, *, scale=None, causal=False, variant=0):
     """attention_fwd that also returns lse2 [B,H,Sq] f32 (log2 of the softmax denominator, scale included): (out, lse2)."""
     _require_cuda(q, k, v)
     B, Sq, H, D = q.shape
-    Sk = k.shape[1]
-    out = torch.empty((B, Sq, H, D), dtype=torch.bfloat16, device=q.device)
     lse = torch.empty((B, H, Sq), dtype=torch.float32, device=q.device)
-    if scale is None:
-        scale = D ** -0.5
-    with torch.cuda.device(q.device):
-        rc = load().b200_attention_fwd_lse(
-            _ptr(q), _ptr(k), _ptr(v), _ptr(out), _ptr(lse), B, Sq, Sk, H, D,
-            q.stride(0), q.stride(1), q.stride(2), k.stride(0), k.stride(1), k.stride(2),
-            v.stride(0), v.stride(1), v.stride(2), out.stride(0), out.stride(1), out.stride(2),
-            float(scale), int(bool(causal)), _stream(q))
-    _check(rc, "b200_attention_fwd_lse")
+    out = attention_fwd(q, k, v, scale=scale, causal=causal, lse=lse, variant=variant)
     return out, lse
 
 
@@ -441,11 +445,15 @@ def sum_partials_to_bf16(partials, bias=None, out=None):
 
 
 # ---------------------------------------------------------------- fused GEMM -> reduce-scatter plumbing
-def gemm_bf16_scatter(a, b, block_ptrs, rows_per_block: int, rot: int, ldc: int, *, b_layout=B_KN):
+def gemm_bf16_scatter(a, b, block_ptrs, rows_per_block: int, rot: int, ldc: int, *, b_layout=B_KN, a_block_stride: int = 0,
+                      M: int = 0, tune=None):
     """a[M,K] @ b -> bf16 rows scattered to ``block_ptrs`` (a CUDA int64 tensor of M/rows_per_block base
-    pointers, e.g. peer GPUs' receive slots): b200_gemm_bf16_ex with the row-block scatter."""
+    pointers, e.g. peer GPUs' receive slots): b200_gemm_bf16_ex with the row-block scatter.  With ``a_block_stride`` > 0
+    block j of the product is read from rows [j * a_block_stride, j * a_block_stride + rows_per_block) of ``a`` (``M`` =
+    logical rows of the product): one token chunk of every owner's row block."""
     _require_cuda(a, b, block_ptrs)
-    M, K = a.shape
+    K = a.shape[1]
+    M = M or a.shape[0]
     N = b.shape[1] if b_layout == B_KN else b.shape[0]
     args = GemmArgs()
     args.A, args.lda = a.data_ptr(), a.stride(0)
@@ -453,7 +461,10 @@ def gemm_bf16_scatter(a, b, block_ptrs, rows_per_block: int, rot: int, ldc: int,
     args.C, args.ldc, args.out_dtype = None, ldc, BF16
     args.c_block_ptrs = block_ptrs.data_ptr()
     args.m_rows_per_block, args.m_block_rot = rows_per_block, rot
+    if a_block_stride:
+        args.a_rows_per_block, args.a_block_stride = rows_per_block, a_block_stride
     args.M, args.N, args.K, args.epilogue = M, N, K, EPI_NONE
+    args.tune = _tuning(tune)
     with torch.cuda.device(a.device):
         rc = load().b200_gemm_bf16_ex(ctypes.byref(args), _stream(a))
     _check(rc, "b200_gemm_bf16_ex")

@@ -337,100 +337,58 @@ static int launch_attention(const void* Q, const void* K, const void* V, const A
   return B200_OK;
 }
 
-int attention_fwd2_dispatch(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
-                            const int64_t* strides, float scale, int causal, cudaStream_t stream);
-int attention_fwd3_dispatch(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
-                            const int64_t* strides, float scale, int causal, cudaStream_t stream);
-int attention_fwd4_dispatch(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
-                            const int64_t* strides, float scale, int causal, cudaStream_t stream);
-int attention_fwd5_dispatch(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
-                            const int64_t* strides, float scale, int causal, cudaStream_t stream);
-int attention_fwd6_dispatch(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
-                            const int64_t* strides, float scale, int causal, cudaStream_t stream);
-int attention_fwd7_dispatch(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
-                            const int64_t* strides, float scale, int causal, cudaStream_t stream);
 int attention_fwd8_dispatch(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
-                            const int64_t* strides, float scale, int causal, cudaStream_t stream);
+                            const int64_t* strides, float scale, int causal, float* lse, cudaStream_t stream);
 int attention_fwd9_dispatch(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
-                            const int64_t* strides, float scale, int causal, cudaStream_t stream);
-// 0 = auto; 1 = one query tile per CTA; 2 = two query tiles, 128-key tiles, P through smem; 3 = two query tiles,
-// 64-key tiles, double-buffered S and P; 4 = two query tiles, 128-key tiles, P kept in TMEM (A operand of P.V);
-// 5 = one query tile, S and P double-buffered in TMEM, softmax rows split over two warp groups;
-// 6 = v5 with Q in TMEM as well (both MMAs take A from TMEM);
-// 7 = one query tile, the two softmax warp groups on alternate KV tiles (whole rows per thread);
-// 8 = v7 as a persistent kernel (one CTA per SM walks a static work list, items overlap);
-// 9 = v8 on CTA pairs (cta_group::2 MMAs, K / V tiles loaded once per 256 query rows), head dim 128 only
-static int g_attn_variant = 0;
-thread_local float* tl_attn_lse = nullptr;
+                            const int64_t* strides, float scale, int causal, float* lse, cudaStream_t stream);
 
 }  // namespace b200
 
 using namespace b200;
 
-namespace b200 { extern long long* g_attn_prof; }
-// bring-up aid: device buffer of >= 8 int64 receiving per-phase cycle totals of one softmax warp (NULL = off)
-extern "C" int b200_attention_set_profile_buffer(void* dev_buf) {
-  b200::g_attn_prof = reinterpret_cast<long long*>(dev_buf);
-  return B200_OK;
-}
-
-extern "C" int b200_attention_set_variant(int variant) {
-  if (variant < 0 || variant > 9) return fail(B200_ERR_INVALID_ARGUMENT, "attention variant must be 0..9");
-  g_attn_variant = variant;
-  return B200_OK;
-}
-
-static int attention_fwd_common(const void* Q, const void* K, const void* V, void* O, float* lse, int B, int Sq, int Sk, int H,
-                                int D, int64_t q_stride_b, int64_t q_stride_s, int64_t q_stride_h,
-                                int64_t k_stride_b, int64_t k_stride_s, int64_t k_stride_h, int64_t v_stride_b,
-                                int64_t v_stride_s, int64_t v_stride_h, int64_t o_stride_b, int64_t o_stride_s,
-                                int64_t o_stride_h, float scale, int causal, void* stream) {
+// Kernels (b200_attention_args.variant): 1 = one 128-row query tile per CTA, blocking schedule (this file);
+// 8 = persistent, one CTA per SM, two softmax warp groups on alternate KV tiles (attention8.cu);
+// 9 = 8 on CTA pairs: cta_group::2 MMAs, K / V tiles loaded once per 256 query rows, head dim 128 only (attention9.cu).
+// Measured predecessors (two query tiles per CTA, 64-key tiles, P through shared memory, ...) are archived under
+// tools/variants/ and are not part of the library.
+extern "C" int b200_attention_fwd_ex(const b200_attention_args* a, void* stream) {
+  B200_REQUIRE(a != nullptr, "b200_attention_fwd: null argument block");
+  const void *Q = a->Q, *K = a->K, *V = a->V;
+  void* O = a->O;
+  const int B = a->B, Sq = a->Sq, Sk = a->Sk, H = a->H, D = a->D, causal = a->causal, variant = a->variant;
   B200_REQUIRE(Q && K && V && O, "b200_attention_fwd: null operand pointer");
   B200_REQUIRE(B > 0 && Sq > 0 && Sk > 0 && H > 0, "b200_attention_fwd: B, Sq, Sk, H must be positive");
   B200_REQUIRE(D == 64 || D == 128, "b200_attention_fwd: head dim must be 64 or 128 (got %d)", D);
   B200_REQUIRE(B <= 65535 && H <= 65535, "b200_attention_fwd: B and H must be <= 65535");
   B200_REQUIRE(!causal || Sk >= Sq, "b200_attention_fwd: causal attention needs Sk >= Sq");
-  const int64_t strides[12] = {q_stride_b, q_stride_s, q_stride_h, k_stride_b, k_stride_s, k_stride_h,
-                               v_stride_b, v_stride_s, v_stride_h, o_stride_b, o_stride_s, o_stride_h};
+  B200_REQUIRE(variant == 0 || variant == 1 || variant == 8 || variant == 9,
+               "b200_attention_fwd: variant must be 0 (auto), 1, 8 or 9 (got %d)", variant);
+  B200_REQUIRE(variant != 9 || D == 128, "b200_attention_fwd: variant 9 (CTA pairs) needs head dim 128");
+  B200_REQUIRE(variant != 1 || a->lse2 == nullptr,
+               "b200_attention_fwd: lse2 is written by the persistent kernels (variant 0, 8, 9)");
+  const int64_t* strides = a->strides;
   for (int i = 0; i < 12; ++i)
     B200_REQUIRE(strides[i] > 0 && strides[i] % 8 == 0, "b200_attention_fwd: strides must be positive multiples of 8");
   B200_REQUIRE((reinterpret_cast<uintptr_t>(Q) | reinterpret_cast<uintptr_t>(K) | reinterpret_cast<uintptr_t>(V) |
                 reinterpret_cast<uintptr_t>(O)) % 16 == 0,
                "b200_attention_fwd: operands must be 16-byte aligned");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  if (lse != nullptr) {
-    // the row log-sum-exp is written by the persistent kernels' epilogue: pairs for head dim 128, single CTAs for 64
-    tl_attn_lse = lse;
-    const int rc = (D == 128 && g_attn_variant != 8)
-                       ? attention_fwd9_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st)
-                       : attention_fwd8_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
-    tl_attn_lse = nullptr;
-    return rc;
-  }
-  if (g_attn_variant == 9) return attention_fwd9_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
-  if (g_attn_variant == 8) return attention_fwd8_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
-  if (g_attn_variant == 7) return attention_fwd7_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
-  if (g_attn_variant == 6) return attention_fwd6_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
-  if (g_attn_variant == 5) return attention_fwd5_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
-  if (g_attn_variant == 4) return attention_fwd4_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
-  if (g_attn_variant == 3) return attention_fwd3_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
-  // auto: measured best per head dim (profiles/r01_attention_v7.md): D = 128 -> v9 (CTA pairs, 1223 TFLOP/s vs 1176 for
-  // v8 and 1084 for v5), D = 64 -> v8 (662 vs 617 for v2); a single query tile stays on v1
-  if (g_attn_variant == 0 && Sq > kAttnBM && D == 128)
-    return attention_fwd9_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
-  if (g_attn_variant == 0 && Sq > kAttnBM && D == 64)
-    return attention_fwd8_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
-  if (g_attn_variant == 2)
-    return attention_fwd2_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, st);
+  const float scale = a->scale;
+  // auto: measured best per head dim (profiles/r01_attention_v7.md): D = 128 -> CTA pairs (1223 TFLOP/s vs 1176 without
+  // pairs), D = 64 -> persistent single CTAs; a single query tile without an lse request stays on the small kernel
+  int v = variant;
+  if (v == 0) v = (Sq > kAttnBM || a->lse2 != nullptr) ? (D == 128 ? 9 : 8) : 1;
+  if (v == 9) return attention_fwd9_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, a->lse2, st);
+  if (v == 8) return attention_fwd8_dispatch(Q, K, V, O, B, Sq, Sk, H, D, strides, scale, causal, a->lse2, st);
   AttnParams p = {};
   p.O = reinterpret_cast<__nv_bfloat16*>(O);
   p.B = B;
   p.Sq = Sq;
   p.Sk = Sk;
   p.H = H;
-  p.o_stride_b = o_stride_b;
-  p.o_stride_s = o_stride_s;
-  p.o_stride_h = o_stride_h;
+  p.o_stride_b = strides[9];
+  p.o_stride_s = strides[10];
+  p.o_stride_h = strides[11];
   p.scale_log2 = scale * 1.4426950408889634f;
   p.causal = causal ? 1 : 0;
   p.num_q_tiles = (Sq + kAttnBM - 1) / kAttnBM;
@@ -438,14 +396,30 @@ static int attention_fwd_common(const void* Q, const void* K, const void* V, voi
   return launch_attention<128>(Q, K, V, p, B, Sq, Sk, H, strides, strides + 3, strides + 6, st);
 }
 
+static int attention_fwd_flat(const void* Q, const void* K, const void* V, void* O, float* lse, int B, int Sq, int Sk, int H,
+                              int D, int64_t q_stride_b, int64_t q_stride_s, int64_t q_stride_h, int64_t k_stride_b,
+                              int64_t k_stride_s, int64_t k_stride_h, int64_t v_stride_b, int64_t v_stride_s,
+                              int64_t v_stride_h, int64_t o_stride_b, int64_t o_stride_s, int64_t o_stride_h, float scale,
+                              int causal, void* stream) {
+  b200_attention_args a = {};
+  a.Q = Q; a.K = K; a.V = V; a.O = O; a.lse2 = lse;
+  a.B = B; a.Sq = Sq; a.Sk = Sk; a.H = H; a.D = D;
+  const int64_t s[12] = {q_stride_b, q_stride_s, q_stride_h, k_stride_b, k_stride_s, k_stride_h,
+                         v_stride_b, v_stride_s, v_stride_h, o_stride_b, o_stride_s, o_stride_h};
+  for (int i = 0; i < 12; ++i) a.strides[i] = s[i];
+  a.scale = scale;
+  a.causal = causal;
+  return b200_attention_fwd_ex(&a, stream);
+}
+
 extern "C" int b200_attention_fwd(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H,
                                   int D, int64_t q_stride_b, int64_t q_stride_s, int64_t q_stride_h,
                                   int64_t k_stride_b, int64_t k_stride_s, int64_t k_stride_h, int64_t v_stride_b,
                                   int64_t v_stride_s, int64_t v_stride_h, int64_t o_stride_b, int64_t o_stride_s,
                                   int64_t o_stride_h, float scale, int causal, void* stream) {
-  return attention_fwd_common(Q, K, V, O, nullptr, B, Sq, Sk, H, D, q_stride_b, q_stride_s, q_stride_h, k_stride_b, k_stride_s,
-                              k_stride_h, v_stride_b, v_stride_s, v_stride_h, o_stride_b, o_stride_s, o_stride_h, scale, causal,
-                              stream);
+  return attention_fwd_flat(Q, K, V, O, nullptr, B, Sq, Sk, H, D, q_stride_b, q_stride_s, q_stride_h, k_stride_b, k_stride_s,
+                            k_stride_h, v_stride_b, v_stride_s, v_stride_h, o_stride_b, o_stride_s, o_stride_h, scale, causal,
+                            stream);
 }
 
 // b200_attention_fwd that also returns, per (batch, head, query row), lse2 = log2(sum_t exp2(log2(e) * scale * s[t])) in
@@ -456,7 +430,7 @@ extern "C" int b200_attention_fwd_lse(const void* Q, const void* K, const void* 
                                       int64_t v_stride_s, int64_t v_stride_h, int64_t o_stride_b, int64_t o_stride_s,
                                       int64_t o_stride_h, float scale, int causal, void* stream) {
   B200_REQUIRE(lse2, "b200_attention_fwd_lse: null lse2");
-  return attention_fwd_common(Q, K, V, O, lse2, B, Sq, Sk, H, D, q_stride_b, q_stride_s, q_stride_h, k_stride_b, k_stride_s,
-                              k_stride_h, v_stride_b, v_stride_s, v_stride_h, o_stride_b, o_stride_s, o_stride_h, scale, causal,
-                              stream);
+  return attention_fwd_flat(Q, K, V, O, lse2, B, Sq, Sk, H, D, q_stride_b, q_stride_s, q_stride_h, k_stride_b, k_stride_s,
+                            k_stride_h, v_stride_b, v_stride_s, v_stride_h, o_stride_b, o_stride_s, o_stride_h, scale, causal,
+                            stream);
 }

@@ -492,10 +492,8 @@ static int launch_attention8(const void* Q, const void* K, const void* V, const 
   return B200_OK;
 }
 
-extern thread_local float* tl_attn_lse;   // set by b200_attention_fwd_lse around the dispatch
-
 int attention_fwd8_dispatch(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
-                            const int64_t* strides, float scale, int causal, cudaStream_t stream) {
+                            const int64_t* strides, float scale, int causal, float* lse, cudaStream_t stream) {
   Attn8Params p = {};
   p.O = reinterpret_cast<__nv_bfloat16*>(O);
   p.Sq = Sq;
@@ -511,7 +509,7 @@ int attention_fwd8_dispatch(const void* Q, const void* K, const void* V, void* O
   const long long total = static_cast<long long>(p.items_per_head) * H * B;
   if (total > 0x7fffffffLL) return fail(B200_ERR_INVALID_ARGUMENT, "b200_attention_fwd: too many work items");
   p.total_items = static_cast<int>(total);
-  p.lse = tl_attn_lse;
+  p.lse = lse;
   if (D == 64) return launch_attention8<64>(Q, K, V, p, B, Sq, Sk, H, strides, strides + 3, strides + 6, stream);
   return launch_attention8<128>(Q, K, V, p, B, Sq, Sk, H, strides, strides + 3, strides + 6, stream);
 }

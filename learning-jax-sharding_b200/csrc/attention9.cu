@@ -705,12 +705,8 @@ static int launch_attention9(const void* Q, const void* K, const void* V, const 
   return B200_OK;
 }
 
-extern long long* g_attn_prof;
-
-extern thread_local float* tl_attn_lse;   // set by b200_attention_fwd_lse around the dispatch
-
 int attention_fwd9_dispatch(const void* Q, const void* K, const void* V, void* O, int B, int Sq, int Sk, int H, int D,
-                            const int64_t* strides, float scale, int causal, cudaStream_t stream) {
+                            const int64_t* strides, float scale, int causal, float* lse, cudaStream_t stream) {
   Attn9Params p = {};
   p.O = reinterpret_cast<__nv_bfloat16*>(O);
   p.Sq = Sq;
@@ -727,8 +723,8 @@ int attention_fwd9_dispatch(const void* Q, const void* K, const void* V, void* O
   const long long total = static_cast<long long>(p.items_per_head) * H * B;
   if (total > 0x7fffffffLL) return fail(B200_ERR_INVALID_ARGUMENT, "b200_attention_fwd: too many work items");
   p.total_items = static_cast<int>(total);
-  p.lse = tl_attn_lse;
-  p.prof = g_attn_prof;
+  p.lse = lse;
+  p.prof = profile_buffer();
   if (D != 128) return fail(B200_ERR_INVALID_ARGUMENT, "attention variant 9 (CTA pairs) needs head dim 128");
   return launch_attention9<128>(Q, K, V, p, B, Sq, Sk, H, strides, strides + 3, strides + 6, stream);
 }

@@ -505,7 +505,6 @@ static int launch_attention_bwd(const void* Q, const void* K, const void* V, con
 }  // namespace b200
 
 using namespace b200;
-namespace b200 { extern long long* g_attn_prof; }
 
 extern "C" int b200_attention_bwd(const b200_attention_bwd_args* a, void* stream) {
   B200_REQUIRE(a, "b200_attention_bwd: null args");
@@ -550,7 +549,7 @@ extern "C" int b200_attention_bwd(const b200_attention_bwd_args* a, void* stream
   p.scale_log2 = a->scale * 1.4426950408889634f;
   p.causal = a->causal ? 1 : 0;
   p.num_q_tiles = (Sq + kBwBM - 1) / kBwBM;
-  p.prof = g_attn_prof;
+  p.prof = profile_buffer();
   int rc = D == 64 ? launch_attention_bwd<64>(a->Q, a->K, a->V, a->O, a->dO, p, delta, B, Sq, Sk, H, a->strides, st)
                    : launch_attention_bwd<128>(a->Q, a->K, a->V, a->O, a->dO, p, delta, B, Sq, Sk, H, a->strides, st);
   if (rc != B200_OK) return rc;

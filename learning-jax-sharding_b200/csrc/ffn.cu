@@ -30,13 +30,16 @@ extern "C" int b200_ffn_fwd(const void* x, const void* W1, const void* b1, const
 // mode, chunks): GEMM1 on all tokens, then per token chunk GEMM2 -> f32 partial -> NCCL all-reduce / reduce-scatter on a
 // side stream -> bf16 (+ b2), so the collective of chunk c runs under GEMM2 of chunk c+1.  The side stream and its events
 // are created once per device (first call = set-up; make it before any stream capture) and joined to `stream` with events,
-// so the call is stream-ordered from outside.  The throughput path of this repo is the fused variant (csrc/peer.cu +
+// so the call is stream-ordered from outside.  Calls on one device are serialised on the host (a per-device mutex around the
+// enqueue), because they share that side stream and its events.  The throughput path of this repo is the fused variant (csrc/peer.cu +
 // b200_gemm_bf16_ex); this entry point is the NCCL form for binders without CUDA-IPC.
 #include <mutex>
 
 namespace {
 constexpr int kMaxChunks = 16;
 struct TpSide {
+  std::mutex call_mu;   // held for the whole enqueue of one call: two host threads on one device cannot interleave their
+                        // cudaEventRecord / cudaStreamWaitEvent pairs on the shared events
   cudaStream_t stream = nullptr;
   cudaEvent_t ready[kMaxChunks] = {nullptr};
   cudaEvent_t done = nullptr;
@@ -78,6 +81,7 @@ extern "C" int b200_ffn_fwd_tp(b200_comm* comm, const void* x, const void* W1, c
   B200_REQUIRE(!act_bias || b1, "b200_ffn_fwd_tp: activation %d needs b1", act);
   TpSide* side = nullptr;
   if (int rc = tp_side(&side)) return rc;
+  std::lock_guard<std::mutex> call_lock(side->call_mu);
   cudaStream_t main_st = reinterpret_cast<cudaStream_t>(stream);
   int rc = b200_gemm_bf16(x, d_model, W1, F, B200_B_KN, act_bias ? b1 : nullptr, h, F, B200_BF16, T, F, d_model, act, stream);
   if (rc != B200_OK) return rc;

@@ -395,16 +395,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 }
 
 // ------------------------------------------------------------------ host side
-static int g_force_cta_group = 0;   // 0 = heuristic; 1 / 2 force (set through b200_gemm_set_tuning)
-static int g_force_bn = 0;
-static int g_group_m = 0;   // 0 = heuristic below
-static int g_max_stages = 0;   // 0 = all the stages that fit
-static int g_k_serpentine = -1;   // -1 = heuristic, 0 / 1 force
-static int g_max_ctas = 0;        // 0 = one CTA per SM; n > 0 leaves SMs free for a collective running beside the GEMM
-
+// No tuning state lives here: overrides of the heuristics arrive with the call (b200_gemm_args.tune).
 template <int BN, int G, bool kBKmajor>
 static int launch_gemm(const void* A, int64_t lda, const void* B, int64_t ldb, const GemmParams& p0,
-                       cudaStream_t stream) {
+                       const b200_gemm_tuning& tune, cudaStream_t stream) {
   using Cfg = GemmCfg<BN, G>;
   GemmParams p = p0;
   p.tiles_m = (p.M + kBM * G - 1) / (kBM * G);
@@ -414,11 +408,11 @@ static int launch_gemm(const void* A, int64_t lda, const void* B, int64_t ldb, c
   // ring lets the CTAs of a wave drift apart in K, which costs L2 locality on the shared A/B panels.
   int stages = Cfg::kStages;
   if (G == 2 && stages > 4) stages = 4;
-  if (g_max_stages > 0 && g_max_stages < stages) stages = g_max_stages;
+  if (tune.max_stages > 0 && tune.max_stages < stages) stages = tune.max_stages;
   p.num_stages = stages;
-  p.k_serpentine = g_k_serpentine >= 0 ? g_k_serpentine : 0;
-  if (g_group_m > 0) {
-    p.group_m = g_group_m;
+  p.k_serpentine = tune.k_serpentine ? 1 : 0;
+  if (tune.group_m > 0) {
+    p.group_m = tune.group_m;
   } else {
     // Raster group (row-blocks that sweep all column-blocks together).  Measured with ncu on the two FFN GEMMs
     // (profiles/r01_gemm_dram_traffic_vs_raster.log): at K = 4096 group 16 reads 0.95 GB from DRAM (8: 1.29,
@@ -458,11 +452,20 @@ static int launch_gemm(const void* A, int64_t lda, const void* B, int64_t ldb, c
     if (rc != B200_OK) return rc;
   }
   auto kern = gemm_bf16_kernel<BN, G, kBKmajor>;
-  B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+  {
+    // the opt-in to > 48 KB of dynamic shared memory is per device and per kernel instantiation: do it once each
+    static std::atomic<bool> smem_opted_in[64];
+    int dev = 0;
+    B200_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !smem_opted_in[dev].load(std::memory_order_acquire)) {
+      B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+      if (dev >= 0 && dev < 64) smem_opted_in[dev].store(true, std::memory_order_release);
+    }
+  }
   const int sms = num_sms();
   const int tiles = p.tiles_m * p.tiles_n;
   int workers = sms / G;
-  if (g_max_ctas > 0 && g_max_ctas / G < workers) workers = g_max_ctas / G > 0 ? g_max_ctas / G : 1;
+  if (tune.max_ctas > 0 && tune.max_ctas / G < workers) workers = tune.max_ctas / G > 0 ? tune.max_ctas / G : 1;
   if (tiles < workers) workers = tiles;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(workers * G);
@@ -483,47 +486,14 @@ static int launch_gemm(const void* A, int64_t lda, const void* B, int64_t ldb, c
 
 template <int BN, int G>
 static int launch_gemm_layout(bool kmajor, const void* A, int64_t lda, const void* B, int64_t ldb,
-                              const GemmParams& p, cudaStream_t stream) {
-  return kmajor ? launch_gemm<BN, G, true>(A, lda, B, ldb, p, stream)
-                : launch_gemm<BN, G, false>(A, lda, B, ldb, p, stream);
+                              const GemmParams& p, const b200_gemm_tuning& tune, cudaStream_t stream) {
+  return kmajor ? launch_gemm<BN, G, true>(A, lda, B, ldb, p, tune, stream)
+                : launch_gemm<BN, G, false>(A, lda, B, ldb, p, tune, stream);
 }
 
 }  // namespace b200
 
 using namespace b200;
-
-extern "C" int b200_gemm_set_tuning(int cta_group, int block_n) {
-  if (cta_group < 0 || cta_group > 2) return fail(B200_ERR_INVALID_ARGUMENT, "cta_group must be 0, 1 or 2");
-  if (block_n != 0 && block_n != 64 && block_n != 128 && block_n != 256)
-    return fail(B200_ERR_INVALID_ARGUMENT, "block_n must be 0, 64, 128 or 256");
-  g_force_cta_group = cta_group;
-  g_force_bn = block_n;
-  return B200_OK;
-}
-
-extern "C" int b200_gemm_set_max_stages(int stages) {
-  if (stages < 0 || stages > 8) return fail(B200_ERR_INVALID_ARGUMENT, "stages must be in [0, 8]");
-  g_max_stages = stages;
-  return B200_OK;
-}
-
-extern "C" int b200_gemm_set_max_ctas(int ctas) {
-  if (ctas < 0 || ctas > 4096) return fail(B200_ERR_INVALID_ARGUMENT, "max_ctas must be in [0, 4096]");
-  g_max_ctas = ctas;
-  return B200_OK;
-}
-
-extern "C" int b200_gemm_set_k_serpentine(int mode) {
-  if (mode < -1 || mode > 1) return fail(B200_ERR_INVALID_ARGUMENT, "k_serpentine must be -1 (auto), 0 or 1");
-  g_k_serpentine = mode;
-  return B200_OK;
-}
-
-extern "C" int b200_gemm_set_group_m(int group_m) {
-  if (group_m < 0 || group_m > 1024) return fail(B200_ERR_INVALID_ARGUMENT, "group_m must be in [0, 1024]");
-  g_group_m = group_m;
-  return B200_OK;
-}
 
 extern "C" int b200_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, int b_layout,
                               const void* bias, void* C, int64_t ldc, int out_dtype, int M, int N, int K,
@@ -565,7 +535,8 @@ extern "C" int b200_gemm_bf16_ex(const b200_gemm_args* args, void* stream) {
     B200_REQUIRE(args->m_rows_per_block % 256 == 0 && M % args->m_rows_per_block == 0,
                  "b200_gemm_bf16: m_rows_per_block must be a multiple of 256 that divides M");
     B200_REQUIRE(out_dtype == B200_BF16, "b200_gemm_bf16: row-block scatter writes bf16 only");
-    B200_REQUIRE(a_rows_per_block == 0, "b200_gemm_bf16: row-block scatter and the row-blocked A view exclude each other");
+    B200_REQUIRE(a_rows_per_block == 0 || a_rows_per_block == args->m_rows_per_block,
+                 "b200_gemm_bf16: with the row-block scatter, a_rows_per_block must be 0 or equal m_rows_per_block");
   } else {
     B200_REQUIRE(!scatter, "b200_gemm_bf16: c_block_ptrs needs m_rows_per_block");
   }
@@ -616,15 +587,22 @@ extern "C" int b200_gemm_bf16_ex(const b200_gemm_args* args, void* stream) {
   if (N <= 64 || tiles_for(128, 128) < sms / 2) bn = 64;
   else if (N <= 128 || tiles_for(128, 256) < sms) bn = 128;
   int g = (bn >= 128 && tiles_for(256, bn) >= sms / 2) ? 2 : 1;
-  if (g_force_bn) bn = g_force_bn;
-  if (g_force_cta_group) g = g_force_cta_group;
+  const b200_gemm_tuning& tune = args->tune;
+  B200_REQUIRE(tune.cta_group >= 0 && tune.cta_group <= 2, "b200_gemm_bf16: tune.cta_group must be 0, 1 or 2");
+  B200_REQUIRE(tune.block_n == 0 || tune.block_n == 64 || tune.block_n == 128 || tune.block_n == 256,
+               "b200_gemm_bf16: tune.block_n must be 0, 64, 128 or 256");
+  B200_REQUIRE(tune.group_m >= 0 && tune.group_m <= 1024 && tune.max_stages >= 0 && tune.max_stages <= 8 &&
+                   tune.max_ctas >= 0 && tune.max_ctas <= 4096,
+               "b200_gemm_bf16: tune.group_m / max_stages / max_ctas out of range");
+  if (tune.block_n) bn = tune.block_n;
+  if (tune.cta_group) g = tune.cta_group;
   if (g == 2 && bn == 64) g = 1;   // a CTA would load 32 B columns: not a whole swizzle chunk
 
   if (g == 2) {
-    if (bn == 256) return launch_gemm_layout<256, 2>(kmajor, A, lda, B, ldb, p, st);
-    return launch_gemm_layout<128, 2>(kmajor, A, lda, B, ldb, p, st);
+    if (bn == 256) return launch_gemm_layout<256, 2>(kmajor, A, lda, B, ldb, p, tune, st);
+    return launch_gemm_layout<128, 2>(kmajor, A, lda, B, ldb, p, tune, st);
   }
-  if (bn == 256) return launch_gemm_layout<256, 1>(kmajor, A, lda, B, ldb, p, st);
-  if (bn == 128) return launch_gemm_layout<128, 1>(kmajor, A, lda, B, ldb, p, st);
-  return launch_gemm_layout<64, 1>(kmajor, A, lda, B, ldb, p, st);
+  if (bn == 256) return launch_gemm_layout<256, 1>(kmajor, A, lda, B, ldb, p, tune, st);
+  if (bn == 128) return launch_gemm_layout<128, 1>(kmajor, A, lda, B, ldb, p, tune, st);
+  return launch_gemm_layout<64, 1>(kmajor, A, lda, B, ldb, p, tune, st);
 }

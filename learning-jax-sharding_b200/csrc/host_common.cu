@@ -86,7 +86,22 @@ int num_sms() {
   return cached[dev];
 }
 
+#ifdef B200_PROFILE_HOOKS
+static long long* g_profile_buffer = nullptr;
+long long* profile_buffer() { return g_profile_buffer; }
+#else
+long long* profile_buffer() { return nullptr; }
+#endif
+
 }  // namespace b200
+
+#ifdef B200_PROFILE_HOOKS
+// bring-up builds only: device buffer of >= 16 int64 receiving per-phase cycle totals (NULL = off)
+extern "C" int b200_attention_set_profile_buffer(void* dev_buf) {
+  b200::g_profile_buffer = reinterpret_cast<long long*>(dev_buf);
+  return B200_OK;
+}
+#endif
 
 extern "C" int b200_version(void) { return B200_VERSION; }
 extern "C" const char* b200_last_error(void) { return b200::error_buffer(); }

@@ -39,4 +39,8 @@ int make_tensor_map(CUtensorMap* out, const void* base, int elem_bytes, int rank
 
 int num_sms();   // SM count of the current device (cached per device)
 
+// Device buffer for the clock64 phase profiles of the attention kernels.  Always NULL unless the library was built with
+// -DB200_PROFILE_HOOKS (a bring-up build: it adds b200_attention_set_profile_buffer, which is process-wide state).
+long long* profile_buffer();
+
 }  // namespace b200

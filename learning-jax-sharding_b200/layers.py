@@ -306,15 +306,14 @@ class FsdpFFN:
             if self.prefetch:
                 self._gather_w1(buf ^ 1)          # for the next call: runs under this call's second GEMM
                 self._w1_inflight = call + 1
-        if self.gemm_max_ctas:
-            capi.set_gemm_max_ctas(self.gemm_max_ctas)
+        tune = {"max_ctas": self.gemm_max_ctas} if self.gemm_max_ctas else None   # travels with each call: no library state
         fc, dc = self.F // C, self.d_model // C
         for j in range(C):
             main.wait_event(self.ready1[buf][j])
             if record is not None:
                 record("start")
             b = self.b1[j * fc:(j + 1) * fc] if self.b1 is not None else None
-            capi.gemm_bf16(x, self.w1g[buf, j], bias=b, epilogue=self.act, out=self.h[:, j * fc:(j + 1) * fc])
+            capi.gemm_bf16(x, self.w1g[buf, j], bias=b, epilogue=self.act, out=self.h[:, j * fc:(j + 1) * fc], tune=tune)
             if record is not None:
                 record("gemm1")
         self.read1[buf].record(main)
@@ -324,12 +323,10 @@ class FsdpFFN:
                 record("start")
             b = self.b2[j * dc:(j + 1) * dc] if self.b2 is not None else None
             capi.gemm_bf16(self.h, self.w2g[buf, j], bias=b, epilogue=capi.EPI_BIAS if b is not None else capi.EPI_NONE,
-                           out=self.y[:, j * dc:(j + 1) * dc])
+                           out=self.y[:, j * dc:(j + 1) * dc], tune=tune)
             if record is not None:
                 record("gemm2")
         self.read2[buf].record(main)
-        if self.gemm_max_ctas:
-            capi.set_gemm_max_ctas(0)
         return self.y
 
 

@@ -1,13 +1,16 @@
 """Parity tests proper (-m gpu): the CUDA path, called through the C ABI (libb200sl.so via ctypes),
 against the CPU oracle on the same seeded inputs and against the committed golden fixtures.
-Tolerances are the ones BASELINE.json's north_star states: fp32 rtol 1e-5; bf16 rtol 2e-2
-(with atol 2e-2 for values near zero) against the fp32-accumulate oracle tier."""
+Tolerances are the ones BASELINE.json's north_star states: fp32 rtol 1e-5; bf16 rtol 2e-2 against the
+fp32-accumulate oracle tier.  Where outputs are O(1) (GEMM / Dense / FFN at small K) the rtol is paired with a flat
+atol 2e-2; the attention kernels, whose outputs shrink with the number of keys, use bounds that scale with the expected
+row (tests/_tol.py): |got - T1| <= 2e-2 |T1| + 4 * 2^-8 * rms_row, and |got - f64| <= |T1 - f64| + 2 bf16 ulp."""
 import os
 
 import pytest
 import torch
 
 from oracle import reference_math as rm
+from tests import _tol
 from tests.golden import make_golden as mg
 
 pytestmark = pytest.mark.gpu
@@ -21,13 +24,17 @@ def _dev(t, dtype=None):
     return t.to(dtype) if dtype is not None else t
 
 
-@pytest.fixture(autouse=True)
-def _default_tuning(ljs):
-    ljs.capi.set_gemm_tuning(0, 0)
-    ljs.capi.set_attention_variant(0)
-    yield
-    ljs.capi.set_gemm_tuning(0, 0)
-    ljs.capi.set_attention_variant(0)
+def _check_attention(o, q, k, v, causal, what, blocked=0):
+    """Both tiers of tests/_tol.py for an attention forward output (CPU tensors)."""
+    if blocked:
+        t1 = rm.attention_core_blocked(q, k, v, causal=causal, q_block=blocked)
+        f64 = rm.attention_core_blocked(q, k, v, causal=causal, q_block=blocked, f64=True)
+    else:
+        t1 = rm.attention_core(q, k, v, causal=causal)
+        f64 = rm.attention_core_f64(q.to(torch.bfloat16).double(), k.to(torch.bfloat16).double(), v.to(torch.bfloat16).double(),
+                                    causal=causal)
+    _tol.assert_close_scaled(o.float(), t1.float(), rtol=2e-2, c=4.0, what=what)
+    _tol.assert_no_further_from_f64(o.float(), t1.float(), f64, ulps=2.0, what=what)
 
 
 # ---------------------------------------------------------------------------- fp32 matmuls
@@ -81,12 +88,12 @@ def test_gemm_f32_shapes(ljs, shape):
 @pytest.mark.parametrize("layout", ["kn", "nk"])
 def test_gemm_bf16_tile_configs(ljs, g, bn, layout):
     capi = ljs.capi
-    capi.set_gemm_tuning(g, bn)
+    tune = {"cta_group": g, "block_n": bn}          # per-call overrides: the library holds no tuning state
     for (M, N, K) in [(128, 256, 64), (384, 640, 192), (1000, 264, 136), (2048, 512, 640)]:
         a = rm.synthetic((M, K), 10).to(torch.bfloat16)
         w = rm.synthetic((K, N), 11, "weight").to(torch.bfloat16)
         bmat = w if layout == "kn" else w.t().contiguous()
-        got = capi.gemm_bf16(_dev(a), _dev(bmat), b_layout=capi.B_KN if layout == "kn" else capi.B_NK).cpu()
+        got = capi.gemm_bf16(_dev(a), _dev(bmat), b_layout=capi.B_KN if layout == "kn" else capi.B_NK, tune=tune).cpu()
         want = rm.dense_bf16(a, w)
         torch.testing.assert_close(got.float(), want.float(), **BF16_TOL)
         # the fp32-accumulate check: at most one bf16 ulp from the once-rounded f32 product
@@ -151,6 +158,32 @@ def test_gemm_bf16_linearity_at_config_size(ljs):
     assert torch.equal(y2, y * 2)
 
 
+@pytest.mark.parametrize("act", ["gelu_tanh", "relu"])
+def test_ffn_config_size_sampled_rows(ljs, act):
+    """The whole FFN at BASELINE.json configs[1] (T = 16384, d_model 4096, d_ff 16384, bias): y = act(x W1 + b1) W2 + b2
+    through b200_ffn_fwd, against the oracle on 64 seeded rows (rows of an FFN are independent).  Covers GEMM2 at
+    K = 16384 and the fused bias + activation epilogue at N = 16384, which the small-shape tests do not reach."""
+    capi = ljs.capi
+    T, d, f = 16384, 4096, 16384
+    x = rm.synthetic((T, d), 0).to(torch.bfloat16)
+    w1, b1 = rm.synthetic((d, f), 1, "weight").to(torch.bfloat16), rm.synthetic((f,), 2, "bias").to(torch.bfloat16)
+    w2, b2 = rm.synthetic((f, d), 3, "weight").to(torch.bfloat16), rm.synthetic((d,), 4, "bias").to(torch.bfloat16)
+    code = capi.EPI_BIAS_GELU_TANH if act == "gelu_tanh" else capi.EPI_BIAS_RELU
+    h = torch.empty((T, f), dtype=torch.bfloat16, device="cuda")
+    y = capi.ffn_fwd(_dev(x), _dev(w1), _dev(b1), _dev(w2), _dev(b2), act=code, h=h)
+    rows = torch.cat([torch.tensor([0, 127, 128, 255, 256, 8191, 8192, 16383]),
+                      torch.randint(0, T, (56,), generator=torch.Generator().manual_seed(7))])
+    want = rm.ffn_forward(x[rows], w1, b1, w2, b2, act)
+    got = y[rows.cuda()].cpu()
+    _tol.assert_close_scaled(got.float(), want.float(), rtol=2e-2, c=4.0, what=f"FFN {act} config size")
+    f64 = rm.ffn_forward_f64(x[rows].double(), w1.double(), b1.double(), w2.double(), b2.double(), act)
+    _tol.assert_no_further_from_f64(got.float(), want.float(), f64, ulps=2.0, what=f"FFN {act} config size")
+    # the intermediate too: h = act(x W1 + b1) on the same rows, bf16 (the fused epilogue at N = 16384)
+    hw = rm.dense_bf16(x[rows], w1, b1).float()
+    hw = torch.relu(hw) if act == "relu" else rm.gelu_tanh(hw).to(torch.bfloat16).float()
+    _tol.assert_close_scaled(h[rows.cuda()].cpu().float(), hw, rtol=2e-2, c=4.0, what=f"FFN {act} hidden")
+
+
 # ------------------------------------------------------------------------------------ FFN
 @pytest.mark.parametrize("act", ["gelu", "relu"])
 def test_ffn_against_golden(ljs, act):
@@ -190,33 +223,35 @@ def test_ffn_sharded_layers_virtual_mesh(ljs):
 def test_attention_against_golden(ljs, d, causal):
     q, k, v = mg.attention_inputs(d)
     o = ljs.capi.attention_fwd(_dev(q), _dev(k), _dev(v), causal=causal).cpu()
-    torch.testing.assert_close(o.float(), GOLD[f"attn_d{d}" + ("_causal" if causal else "")].float(), **BF16_TOL)
+    _tol.assert_close_scaled(o.float(), GOLD[f"attn_d{d}" + ("_causal" if causal else "")].float(), rtol=2e-2, c=4.0,
+                             what=f"attention golden d{d}")
+    _check_attention(o, q, k, v, causal, f"attention golden d{d}")
 
 
 @pytest.mark.parametrize("shape", [(1, 1, 1, 1, 64), (1, 5, 300, 2, 64), (2, 128, 128, 3, 128), (1, 257, 257, 2, 128),
                                    (2, 100, 1000, 2, 64), (1, 1024, 1024, 4, 128), (1, 384, 640, 2, 128),
                                    (1, 1300, 1300, 1, 64)])
 @pytest.mark.parametrize("causal", [False, True])
-@pytest.mark.parametrize("variant", [1, 2, 3, 4, 5, 6, 7, 8, 9])
+@pytest.mark.parametrize("variant", [0, 1, 8, 9])
 def test_attention_ragged_shapes(ljs, shape, causal, variant):
-    ljs.capi.set_attention_variant(variant)      # 1 = one query tile per CTA, 2 / 3 = two tiles (128- / 64-key KV tiles)
+    """Every kernel of the library (variant is a per-call argument: 0 = library choice, 1 = one query tile per CTA,
+    8 = persistent, 9 = persistent CTA pairs) on ragged Sq / Sk, both tolerance tiers."""
     B, Sq, Sk, H, D = shape
     if variant == 9 and D != 128:
         pytest.skip("variant 9 (CTA pairs) is head dim 128 only")
     q = rm.synthetic((B, Sq, H, D), 40).to(torch.bfloat16)
     k = rm.synthetic((B, Sk, H, D), 41).to(torch.bfloat16)
     v = rm.synthetic((B, Sk, H, D), 42).to(torch.bfloat16)
-    o = ljs.capi.attention_fwd(_dev(q), _dev(k), _dev(v), causal=causal).cpu()
-    torch.testing.assert_close(o.float(), rm.attention_core(q, k, v, causal=causal).float(), **BF16_TOL)
+    o = ljs.capi.attention_fwd(_dev(q), _dev(k), _dev(v), causal=causal, variant=variant).cpu()
+    _check_attention(o, q, k, v, causal, f"attention v{variant} {shape} causal={causal}")
 
 
-@pytest.mark.parametrize("variant", [2, 5, 7, 8, 9])
+@pytest.mark.parametrize("variant", [8, 9])
 @pytest.mark.parametrize("causal", [False, True])
 @pytest.mark.parametrize("ramp_top", [24.0, 2.0, 1.0])   # every row rescales in every tile / 90-99 % of rows / alternate tiles
 def test_attention_growing_row_max(ljs, variant, causal, ramp_top):
     """Logits that grow along the key axis: the running max rises by more than the lazy-rescale threshold (2^8) several
-    times per row, in even and in odd KV tiles, so O is rescaled in TMEM by either softmax group of variant 7."""
-    ljs.capi.set_attention_variant(variant)
+    times per row, in even and in odd KV tiles, so O is rescaled in TMEM by either softmax group."""
     B, S, H, D = 1, 1024, 2, 128
     q = rm.synthetic((B, S, H, D), 60).to(torch.bfloat16)
     k = rm.synthetic((B, S, H, D), 61).to(torch.bfloat16)
@@ -224,9 +259,8 @@ def test_attention_growing_row_max(ljs, variant, causal, ramp_top):
     ramp = torch.linspace(0.0, ramp_top, S).view(1, S, 1, 1)
     q = (q.float().abs() + 0.5).to(torch.bfloat16)                     # positive queries ...
     k = (k.float().abs() * ramp + ramp).to(torch.bfloat16)             # ... against keys whose size grows with position
-    o = ljs.capi.attention_fwd(_dev(q), _dev(k), _dev(v), causal=causal).cpu()
-    assert torch.isfinite(o.float()).all()
-    torch.testing.assert_close(o.float(), rm.attention_core(q, k, v, causal=causal).float(), **BF16_TOL)
+    o = ljs.capi.attention_fwd(_dev(q), _dev(k), _dev(v), causal=causal, variant=variant).cpu()
+    _check_attention(o, q, k, v, causal, f"attention v{variant} ramp {ramp_top} causal={causal}")
 
 
 def test_attention_properties(ljs):
@@ -236,35 +270,47 @@ def test_attention_properties(ljs):
     # uniform V: softmax rows sum to one, so O == V
     ones = torch.full((2, 512, 4, 128), 0.5, dtype=torch.bfloat16)
     o = capi.attention_fwd(_dev(q), _dev(k), _dev(ones)).cpu()
-    torch.testing.assert_close(o.float(), ones.float(), rtol=1e-2, atol=1e-2)
+    torch.testing.assert_close(o.float(), ones.float(), rtol=2 ** -7, atol=0)
     # causal row 0 attends to key 0 only
     v = rm.synthetic((2, 512, 4, 128), 52).to(torch.bfloat16)
     o = capi.attention_fwd(_dev(q), _dev(k), _dev(v), causal=True).cpu()
     assert torch.equal(o[:, 0], v[:, 0])
     # large logits: the running max keeps exp in range
     o = capi.attention_fwd(_dev(q * 16), _dev(k * 16), _dev(v)).cpu()
-    assert torch.isfinite(o.float()).all()
-    torch.testing.assert_close(o.float(), rm.attention_core(q * 16, k * 16, v).float(), **BF16_TOL)
+    _check_attention(o, q * 16, k * 16, v, False, "attention large logits")
     # strided input: q/k/v as slices of one fused projection buffer [B, S, 3*H*D]
     qkv = torch.cat([q.reshape(2, 512, -1), k.reshape(2, 512, -1), v.reshape(2, 512, -1)], dim=-1).cuda()
     qs, ks, vs = (qkv[..., i * 512:(i + 1) * 512].view(2, 512, 4, 128) for i in range(3))
     o2 = capi.attention_fwd(qs, ks, vs).cpu()
-    torch.testing.assert_close(o2.float(), rm.attention_core(q, k, v).float(), **BF16_TOL)
+    _check_attention(o2, q, k, v, False, "attention strided views")
 
 
-def test_attention_config_size_sample(ljs):
-    """BASELINE.json case5 shape (B8, S4096, 32 heads x 128): the oracle on a seeded sample of
-    (batch, head) pairs -- heads and batch items are independent."""
+def test_attention_rejects_bad_variant(ljs):
+    q = torch.zeros((1, 256, 1, 64), dtype=torch.bfloat16, device="cuda")
+    with pytest.raises(ljs.capi.B200Error, match="variant"):
+        ljs.capi.attention_fwd(q, q, q, variant=5)          # the archived experiments are not in the library
+    with pytest.raises(ljs.capi.B200Error, match="head dim 128"):
+        ljs.capi.attention_fwd(q, q, q, variant=9)
+
+
+@pytest.mark.parametrize("cfg", ["case5", "case6"])
+def test_attention_config_size_sample(ljs, cfg):
+    """BASELINE.json attention shapes -- case5: B8, S4096, 32 heads x 128, non-causal (and causal); case6: B16, S8192,
+    32 x 128, causal, on the heads one GPU of the 2x4 mesh holds (batch 8, 8 heads).  The oracle runs on a seeded sample
+    of (batch, head) pairs: heads and batch items are independent.  Both tolerance tiers."""
     capi = ljs.capi
-    B, S, H, D = 8, 4096, 32, 128
+    if cfg == "case5":
+        B, S, H, D, modes, pairs = 8, 4096, 32, 128, (False, True), [(0, 0), (3, 17), (7, 31)]
+    else:
+        B, S, H, D, modes, pairs = 8, 8192, 8, 128, (True,), [(0, 0), (5, 3), (7, 7)]
     g = torch.Generator(device="cuda").manual_seed(3)
     q, k, v = (torch.randn(B, S, H, D, device="cuda", generator=g).to(torch.bfloat16) for _ in range(3))
-    for causal in (False, True):
+    for causal in modes:
         o = capi.attention_fwd(q, k, v, causal=causal)
-        for (b, h) in [(0, 0), (3, 17), (7, 31)]:
+        for (b, h) in pairs:
             sl = (slice(b, b + 1), slice(None), slice(h, h + 1))
-            want = rm.attention_core_blocked(q[sl].cpu(), k[sl].cpu(), v[sl].cpu(), causal=causal, q_block=1024)
-            torch.testing.assert_close(o[sl].cpu().float(), want.float(), **BF16_TOL)
+            _check_attention(o[sl].cpu(), q[sl].cpu(), k[sl].cpu(), v[sl].cpu(), causal,
+                             f"{cfg} config size (b={b}, h={h}, causal={causal})", blocked=1024)
 
 
 # ------------------------------------------------------------------- literal case5 / case6
@@ -458,7 +504,10 @@ def test_dense_train_step_literal_case5(ljs, wspec):
 
 
 # ------------------------------------------------------------------------------ attention backward (8f row 1)
-GRAD_TOL = dict(rtol=3e-2, atol=3e-2)
+def _check_grads(got, want_bf16, want_f64, what):
+    """Both tiers of tests/_tol.py for one gradient tensor; rtol 2e-2 (north_star), absolute term scaled by the row."""
+    _tol.assert_close_scaled(got.float(), want_bf16.float(), rtol=2e-2, c=6.0, what=what)
+    _tol.assert_no_further_from_f64(got.float(), want_bf16.float(), want_f64, ulps=3.0, what=what)
 
 
 @pytest.mark.parametrize("shape", [(1, 128, 128, 1, 64), (1, 128, 128, 1, 128), (2, 256, 256, 2, 128), (1, 200, 333, 2, 64),
@@ -473,13 +522,14 @@ def test_attention_backward_matches_oracle(ljs, shape, causal):
     v = rm.synthetic((B, Sk, H, D), 92).to(torch.bfloat16)
     do = rm.synthetic((B, Sq, H, D), 93).to(torch.bfloat16)
     dq_w, dk_w, dv_w, lse_w = rm.attention_core_grads(q, k, v, do, causal=causal)
+    dq_e, dk_e, dv_e, _ = rm.attention_core_grads(q, k, v, do, causal=causal, rounded=False)
     o, lse = ljs.capi.attention_fwd_lse(_dev(q), _dev(k), _dev(v), causal=causal)
-    torch.testing.assert_close(o.cpu().float(), rm.attention_core(q, k, v, causal=causal).float(), **BF16_TOL)
-    torch.testing.assert_close(lse.cpu(), lse_w, rtol=1e-3, atol=2e-2)
+    _check_attention(o.cpu(), q, k, v, causal, f"attention fwd_lse {shape}")
+    torch.testing.assert_close(lse.cpu(), lse_w, rtol=0, atol=4e-3)      # log2 units: a 0.3 % error of the denominator
     dq, dk, dv = ljs.capi.attention_bwd(_dev(q), _dev(k), _dev(v), o, _dev(do), lse, causal=causal)
-    torch.testing.assert_close(dv.cpu().float(), dv_w.float(), **GRAD_TOL)
-    torch.testing.assert_close(dk.cpu().float(), dk_w.float(), **GRAD_TOL)
-    torch.testing.assert_close(dq.cpu().float(), dq_w.float(), **GRAD_TOL)
+    _check_grads(dv.cpu(), dv_w, dv_e, f"dV {shape} causal={causal}")
+    _check_grads(dk.cpu(), dk_w, dk_e, f"dK {shape} causal={causal}")
+    _check_grads(dq.cpu(), dq_w, dq_e, f"dQ {shape} causal={causal}")
 
 
 def test_attention_backward_properties(ljs):
@@ -491,8 +541,28 @@ def test_attention_backward_properties(ljs):
     v = torch.full((B, S, H, D), 0.5, dtype=torch.bfloat16, device="cuda")
     o, lse = ljs.capi.attention_fwd_lse(q, k, v)
     dq, dk, dv = ljs.capi.attention_bwd(q, k, v, o, do, lse)
-    assert dq.float().abs().max().item() < 2e-2 and dk.float().abs().max().item() < 2e-2
+    # with random V at this shape |dQ|, |dK| ~ 0.04-0.09 (rms); here they must vanish up to bf16 rounding of dS
+    assert dq.float().abs().max().item() < 2e-3 and dk.float().abs().max().item() < 2e-3
     torch.testing.assert_close(dv.float().sum(1), do.float().sum(1), rtol=2e-2, atol=0.5)
+
+
+@pytest.mark.parametrize("causal", [False, True])
+def test_attention_backward_config_size_sample(ljs, causal):
+    """dQ, dK, dV at a config-size sequence (S = 4096, head dim 128) against autodiff of the f64 formula on sampled
+    (batch, head) pairs; both tolerance tiers."""
+    B, S, H, D = 2, 4096, 4, 128
+    g = torch.Generator(device="cuda").manual_seed(11)
+    q, k, v, do = (torch.randn(B, S, H, D, device="cuda", generator=g).to(torch.bfloat16) for _ in range(4))
+    o, lse = ljs.capi.attention_fwd_lse(q, k, v, causal=causal)
+    dq, dk, dv = ljs.capi.attention_bwd(q, k, v, o, do, lse, causal=causal)
+    for (b, h) in [(0, 0), (1, 3)]:
+        sl = (slice(b, b + 1), slice(None), slice(h, h + 1))
+        args = (q[sl].cpu(), k[sl].cpu(), v[sl].cpu(), do[sl].cpu())
+        dq_w, dk_w, dv_w, _ = rm.attention_core_grads(*args, causal=causal)
+        dq_e, dk_e, dv_e, _ = rm.attention_core_grads(*args, causal=causal, rounded=False)
+        _check_grads(dv[sl].cpu(), dv_w, dv_e, f"dV S4096 (b={b}, h={h}) causal={causal}")
+        _check_grads(dk[sl].cpu(), dk_w, dk_e, f"dK S4096 (b={b}, h={h}) causal={causal}")
+        _check_grads(dq[sl].cpu(), dq_w, dq_e, f"dQ S4096 (b={b}, h={h}) causal={causal}")
 
 
 @pytest.mark.parametrize("causal", [False, True])

@@ -19,6 +19,20 @@ spec = importlib.util.spec_from_file_location("capi", os.path.join(ROOT, "learni
 capi = importlib.util.module_from_spec(spec)
 spec.loader.exec_module(capi)
 
+# The library keeps no tuning state (overrides travel with each call: b200_gemm_args.tune, b200_attention_args.variant).
+# This tool's sweeps were written as "set, then call": the setters below only edit TOOL-LOCAL dictionaries that the wrapped
+# call functions pass along.
+_TUNE, _ATTN = {}, {"variant": 0}
+_gemm_bf16, _attention_fwd, _attention_fwd_lse = capi.gemm_bf16, capi.attention_fwd, capi.attention_fwd_lse
+capi.gemm_bf16 = lambda *a, **k: _gemm_bf16(*a, **{"tune": dict(_TUNE), **k})
+capi.attention_fwd = lambda *a, **k: _attention_fwd(*a, **{"variant": _ATTN["variant"], **k})
+capi.attention_fwd_lse = lambda *a, **k: _attention_fwd_lse(*a, **{"variant": _ATTN["variant"], **k})
+capi.set_gemm_tuning = lambda g=0, bn=0: _TUNE.update(cta_group=g, block_n=bn)
+capi.set_gemm_group_m = lambda gm=0: _TUNE.update(group_m=gm)
+capi.set_gemm_k_serpentine = lambda mode=-1: _TUNE.update(k_serpentine=1 if mode == 1 else 0)
+capi.set_gemm_max_stages = lambda st=0: _TUNE.update(max_stages=st)
+capi.set_attention_variant = lambda v=0: _ATTN.update(variant=v)     # 0, 1, 8, 9 (2-7 are archived in tools/variants/)
+
 
 def ref_epilogue(acc, bias, epi):
     v = acc.to(torch.bfloat16).float()
@@ -174,7 +188,6 @@ def main():
     elif args.what == "gemm_stages":
         import ctypes
         lib = capi.load()
-        lib.b200_gemm_set_max_stages.argtypes = [ctypes.c_int]
         import statistics
         for (M, N, K) in [(16384, 16384, 4096), (16384, 4096, 16384)]:
             a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
@@ -189,19 +202,18 @@ def main():
                         ms = time_fn(lambda: torch.matmul(a, b, out=out), iters=10, warmup=2)
                     else:
                         capi.set_gemm_tuning(g, bn)
-                        lib.b200_gemm_set_max_stages(st)
+                        capi.set_gemm_max_stages(st)
                         ms = time_fn(lambda: capi.gemm_bf16(a, b, out=out), iters=10, warmup=2)
                     res[v].append(ms)
             for v in variants:
                 ms = statistics.median(res[v])
                 name = "cublas" if v[2] < 0 else f"g={v[0]} bn={v[1]} stages={v[2]}"
                 print(f"  {name:24s} M={M} N={N} K={K}: {ms:.3f} ms {2 * M * N * K / ms / 1e9:.1f} TFLOP/s", flush=True)
-            lib.b200_gemm_set_max_stages(0)
+            capi.set_gemm_max_stages(0)
     elif args.what == "gemm_sweep2":
         import ctypes
         import statistics
         lib = capi.load()
-        lib.b200_gemm_set_max_stages.argtypes = [ctypes.c_int]
         for (M, N, K) in [(16384, 16384, 4096), (16384, 4096, 16384), (32768, 12288, 4096), (8192, 8192, 8192)]:
             a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
             b = torch.randn(K, N, device="cuda").to(torch.bfloat16)
@@ -216,14 +228,14 @@ def main():
                     else:
                         capi.set_gemm_tuning(g, bn)
                         capi.set_gemm_group_m(gm)
-                        lib.b200_gemm_set_max_stages(st)
+                        capi.set_gemm_max_stages(st)
                         ms = time_fn(lambda: capi.gemm_bf16(a, b, out=out), iters=10, warmup=2)
                     res[v].append(ms)
             for v in variants:
                 ms = statistics.median(res[v])
                 name = "cublas" if v[2] < 0 else f"g={v[0]} bn={v[1]} stages={v[2]} group_m={v[3]}"
                 print(f"  {name:36s} M={M} N={N} K={K}: {ms:.3f} ms {2 * M * N * K / ms / 1e9:.1f} TFLOP/s", flush=True)
-            lib.b200_gemm_set_max_stages(0)
+            capi.set_gemm_max_stages(0)
             capi.set_gemm_group_m(0)
     elif args.what == "attn_phases":
         # needs a build with B200_EXTRA_NVCC_FLAGS=-DB200_ATTN_PROFILE=1 (the hooks are compiled out by default)
