@@ -111,17 +111,28 @@ class PeerReduceScatter:
     """Receive side of the fused GEMM -> reduce-scatter for a row-parallel layer with T rows and N output
     features over the W ranks of `group`: CUDA-IPC-shared receive buffers (two, alternating per step, each
     W slots of [T/W, N] bf16), a table of every owner's slot pointers for the GEMM epilogue to push into,
-    a flag barrier and the local f32 reduction of the W received partials."""
+    a flag barrier and the local f32 reduction of the W received partials.
+
+    `chunks` = 2 (default when T/W splits into two multiples of 256 rows) pipelines the tail: the product is
+    pushed as two GEMM launches, each covering HALF of every owner's row block, and the barrier + reduction
+    of the first half run on a side stream underneath the second GEMM, so only half of the reduction (and one
+    barrier) is left after the last GEMM tile.  The side stream is joined before `finish` returns: from outside
+    the call stays ordered on the caller's stream."""
 
     _FLAG_BYTES = 1024
 
-    def __init__(self, T: int, N: int, group, device):
+    def __init__(self, T: int, N: int, group, device, chunks: int = 2):
         import torch.distributed as dist
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         W = self.world
         if T % W or (T // W) % 256:
             raise ValueError(f"T={T} must split into {W} blocks of a multiple of 256 rows")
         self.T, self.N, self.R = T, N, T // W
+        chunks = int(os.environ.get("B200_TP_CHUNKS", chunks))
+        while chunks > 1 and (self.R % chunks or (self.R // chunks) % 256):
+            chunks -= 1
+        self.chunks = max(chunks, 1)
+        self.Rc = self.R // self.chunks                         # rows of one chunk inside one owner's block
         self.slot = self.R * N                                  # elements of one receive slot
         total = self._FLAG_BYTES + 2 * W * self.slot * 2        # flags + two receive buffers of W slots
         self.base, handle = capi.peer_alloc(total)
@@ -131,24 +142,73 @@ class PeerReduceScatter:
         self.peer_base = [self.base if p == self.rank else capi.peer_open(bytes(handles[p].cpu().tolist()))
                           for p in range(W)]
         self.flag_ptrs = torch.tensor(self.peer_base, dtype=torch.int64, device=device)
+        # c_ptrs[buf][chunk][p]: where this rank's partial rows of (owner p, chunk) go in p's memory
         self.c_ptrs = []
         for buf in range(2):
-            ptrs = [self.peer_base[p] + self._FLAG_BYTES + ((buf * W + self.rank) * self.slot) * 2 for p in range(W)]
-            self.c_ptrs.append(torch.tensor(ptrs, dtype=torch.int64, device=device))
+            per_chunk = []
+            for c in range(self.chunks):
+                ptrs = [self.peer_base[p] + self._FLAG_BYTES + ((buf * W + self.rank) * self.slot + c * self.Rc * N) * 2
+                        for p in range(W)]
+                per_chunk.append(torch.tensor(ptrs, dtype=torch.int64, device=device))
+            self.c_ptrs.append(per_chunk)
         self.buf = 0
         self.epoch = 0
+        self.side = torch.cuda.Stream(device=device) if self.chunks > 1 else None
+        self.pushed = [torch.cuda.Event() for _ in range(self.chunks)]
+        self.reduced = torch.cuda.Event()
         dist.barrier(group=group)
 
+    def _push(self, a: torch.Tensor, w: torch.Tensor, c: int):
+        if self.chunks == 1:
+            capi.gemm_bf16_scatter(a, w, self.c_ptrs[self.buf][0], self.R, (self.rank + 1) % self.world, self.N)
+        else:
+            # logical block j of this launch = rows [c*Rc, (c+1)*Rc) of owner j's row block of `a`
+            capi.gemm_bf16_scatter(a[c * self.Rc:], w, self.c_ptrs[self.buf][c], self.Rc, (self.rank + 1) % self.world,
+                                   self.N, a_block_stride=self.R, M=self.world * self.Rc)
+
+    def _reduce(self, c: int, bias, out: torch.Tensor):
+        """Barrier (every rank's pushes of chunk c have landed), then out rows of chunk c = bf16(sum of the W partials)."""
+        self.epoch += 1
+        capi.peer_barrier(self.flag_ptrs, self.rank, self.world, self.epoch)
+        src = self.base + self._FLAG_BYTES + (self.buf * self.world * self.slot + c * self.Rc * self.N) * 2
+        capi.sum_bf16_partials(src, self.slot, self.world, bias, self.N, out[c * self.Rc:(c + 1) * self.Rc])
+
+    def push_and_reduce(self, a: torch.Tensor, w: torch.Tensor, bias, out: torch.Tensor, record=None) -> torch.Tensor:
+        """out[T/W, N] = this rank's row block of sum over ranks of (a @ w) (+ bias): the partial product is stored into
+        the owners' receive slots from the GEMM epilogue (NVLink), reduced locally after a flag barrier."""
+        main = torch.cuda.current_stream(a.device)
+        for c in range(self.chunks):
+            self._push(a, w, c)
+            if record is not None:
+                record("gemm2")
+                if c + 1 < self.chunks:
+                    record("start")
+            if c + 1 < self.chunks:
+                self.pushed[c].record(main)
+                with torch.cuda.stream(self.side):
+                    self.side.wait_event(self.pushed[c])
+                    self._reduce(c, bias, out)
+                    if c + 2 == self.chunks:
+                        self.reduced.record(self.side)
+            else:
+                self._reduce(c, bias, out)
+                if record is not None:
+                    record("reduce")
+        if self.chunks > 1:
+            main.wait_event(self.reduced)
+        self.buf ^= 1
+        return out
+
+    # the two halves separately (single chunk): kept for callers that interleave other work
     def push_gemm(self, a: torch.Tensor, w: torch.Tensor):
         """Partial product a @ w with every finished tile stored into its owner's receive slot (NVLink)."""
-        capi.gemm_bf16_scatter(a, w, self.c_ptrs[self.buf], self.R, (self.rank + 1) % self.world, self.N)
+        if self.chunks != 1:
+            raise RuntimeError("push_gemm / finish are the single-chunk form; use push_and_reduce")
+        self._push(a, w, 0)
 
     def finish(self, bias, out: torch.Tensor) -> torch.Tensor:
         """Barrier (all pushes landed), then out[T/W, N] = bf16(sum of the W partials) (+ bias)."""
-        self.epoch += 1
-        capi.peer_barrier(self.flag_ptrs, self.rank, self.world, self.epoch)
-        src = self.base + self._FLAG_BYTES + (self.buf * self.world * self.slot) * 2
-        capi.sum_bf16_partials(src, self.slot, self.world, bias, self.N, out)
+        self._reduce(0, bias, out)
         self.buf ^= 1
         return out
 
@@ -178,10 +238,7 @@ class FusedTensorParallelFFN:
         capi.gemm_bf16(x, self.w1, bias=self.b1, epilogue=self.act, out=self.h)
         if record is not None:
             record("gemm1")
-        self.rs.push_gemm(self.h, self.w2)
-        if record is not None:
-            record("gemm2")
-        return self.rs.finish(self.b2, self.y)
+        return self.rs.push_and_reduce(self.h, self.w2, self.b2, self.y, record=record)
 
 
 class ShardedMHA:
@@ -228,8 +285,7 @@ class ShardedMHA:
         if self.rs is None:
             capi.gemm_bf16(self.o, self.wo, bias=self.bo, epilogue=capi.EPI_BIAS, out=self.y)           # :139
         else:
-            self.rs.push_gemm(self.o, self.wo)
-            self.rs.finish(self.bo, self.y)
+            self.rs.push_and_reduce(self.o, self.wo, self.bo, self.y)
         if record is not None:
             record("out")
         return self.y
