@@ -218,16 +218,17 @@ class FusedTensorParallelFFN:
     of the partial y is stored from the GEMM epilogue straight into its owner's receive slot over NVLink
     (CUDA-IPC-mapped peer memory), ranks staggered so each destination has one sender at a time; then a
     flag barrier and one local pass summing the W received bf16 partials in f32 (+ b2).  No NCCL on the
-    data path, no token chunking (both GEMMs run at full size).  Same result layout as
+    data path; the first GEMM runs at full size, the second as two launches (half of every owner's block each)
+    so that the barrier + reduction of the first half hide under the second (PeerReduceScatter).  Same result layout as
     TensorParallelFFN: this rank's sequence block y[rank*T/W : (rank+1)*T/W]."""
 
-    def __init__(self, w1, b1, w2, b2, act: str, T: int, group):
+    def __init__(self, w1, b1, w2, b2, act: str, T: int, group, chunks: int = 2):
         self.w1, self.b1, self.w2, self.b2 = w1, b1, w2, b2
         self.act = _act_code(act, b1 is not None)
         self.d_model, self.F = w1.shape
         self.T = T
         dev = w1.device
-        self.rs = PeerReduceScatter(T, self.d_model, group, dev)
+        self.rs = PeerReduceScatter(T, self.d_model, group, dev, chunks=chunks)
         self.world, self.rank = self.rs.world, self.rs.rank
         self.h = torch.empty((T, self.F), dtype=torch.bfloat16, device=dev)
         self.y = torch.empty((self.rs.R, self.d_model), dtype=torch.bfloat16, device=dev)

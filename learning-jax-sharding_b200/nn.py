@@ -119,7 +119,8 @@ def dense(x: ShardedArray, kernel: ShardedArray, bias: Optional[ShardedArray] = 
     rows, kx = xa[:-1], xa[-1]
     row_axes = {a for r in rows for a in r}
     # y's feature dim cannot reuse a mesh axis the rows of x already use: gather the kernel there
-    nw_eff = tuple(a for a in nw if a not in row_axes)
+    # ... nor the axis x's own feature dim is split over (a PartitionSpec may name a mesh axis once)
+    nw_eff = tuple(a for a in nw if a not in row_axes and a not in kx)
     if nw_eff != nw:
         kernel = reshard(kernel, NamedSharding(mesh, _spec([kw, nw_eff])))
     if kx and kw and kx != kw:

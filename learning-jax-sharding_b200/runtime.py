@@ -173,8 +173,9 @@ def _intersect(a, b):
 def _fill_from_sources(dst, want, bufs, src_index) -> bool:
     """Copy into ``dst`` (global slice ``want``) every overlapping piece of the source shards.
     Returns True when the whole of ``want`` was covered."""
-    covered = torch.zeros(dst.shape, dtype=torch.bool) if dst.numel() <= (1 << 22) else None
-    count = 0
+    # coverage is tracked on the destination's own device, whatever the size: a reshard whose sources cover the wanted
+    # slice only partly must fail, never return uninitialised memory
+    covered = torch.zeros(dst.shape, dtype=torch.bool, device=dst.device)
     for s, idx in src_index.items():
         if s not in bufs:
             continue
@@ -184,12 +185,8 @@ def _fill_from_sources(dst, want, bufs, src_index) -> bool:
         dsl = tuple(slice(i.start - w.start, i.stop - w.start) for i, w in zip(inter, want))
         ssl = tuple(slice(i.start - x.start, i.stop - x.start) for i, x in zip(inter, idx))
         dst[dsl].copy_(bufs[s][ssl])
-        if covered is not None:
-            covered[dsl] = True
-        count += 1
-    if covered is not None:
-        return bool(covered.all())
-    return count > 0
+        covered[dsl] = True
+    return bool(covered.all())
 
 
 class DistributedRuntime:

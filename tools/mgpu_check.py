@@ -51,8 +51,20 @@ def main():
     blk = T // world
     err = (y.cpu().float() - want[rank * blk:(rank + 1) * blk]).abs()
     good = bool((err <= 2e-2 * want[rank * blk:(rank + 1) * blk].abs() + 2e-2).all())
-    print(f"[rank {rank}] fused TP (peer-memory push): max_abs={err.max().item():.3e} {'OK' if good else 'FAIL'}", flush=True)
+    print(f"[rank {rank}] fused TP (peer-memory push, {fused.rs.chunks} chunk(s)): max_abs={err.max().item():.3e} "
+          f"{'OK' if good else 'FAIL'}", flush=True)
     ok &= good
+    # the single-launch form gives the same bits (same tiles, same reduction order), and the chunked one is not slower
+    fused1 = layers.FusedTensorParallelFFN(bf(w1[:, rank * fl:(rank + 1) * fl].contiguous()), bf(b1[rank * fl:(rank + 1) * fl]),
+                                           bf(w2[rank * fl:(rank + 1) * fl].contiguous()), bf(b2), "gelu_tanh", T,
+                                           dist.group.WORLD, chunks=1)
+    for it in range(3):
+        y1 = fused1.forward(bf(x))
+    torch.cuda.synchronize()
+    good = bool(torch.equal(y1, y))
+    print(f"[rank {rank}] fused TP chunks=1 vs chunks={fused.rs.chunks}: {'identical' if good else 'DIFFERENT'}", flush=True)
+    ok &= good
+    del fused1
     # head-sharded MHA layer: fused qkv GEMM, local-head attention, row-parallel out-projection with the push reduce-scatter
     Bm, Sm, Mm, Hm, Dm = 2, 1024, 512, 8, 64
     xm = rm.synthetic((Bm, Sm, Mm), 20)
