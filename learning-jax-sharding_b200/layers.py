@@ -523,7 +523,7 @@ class FFNBench:
     functions bench.py times: `step_resident` (inputs in HBM) and `step_e2e` (x from pinned host
     memory, y back to pinned host memory, in token chunks so copies overlap the GEMMs)."""
 
-    def __init__(self, cfg, act, rank, world, dev, chunks=4):
+    def __init__(self, cfg, act, rank, world, dev, chunks=4, host_tensors=None):
         self.cfg, self.rank, self.world, self.dev = cfg, rank, world, dev
         T, d, f = cfg["batch"] * cfg["seq"], cfg["d_model"], cfg["d_ff"]
         self.T, self.d, self.f = T, d, f
@@ -534,11 +534,16 @@ class FFNBench:
             import torch.distributed as dist
             group = dist.group.WORLD
             self._dist = dist
-        x = _synthetic((T, d), 0, "activation").to(torch.bfloat16)
-        w1 = _synthetic((d, f), 1, "weight").to(torch.bfloat16)
-        b1 = _synthetic((f,), 2, "bias").to(torch.bfloat16)
-        w2 = _synthetic((f, d), 3, "weight").to(torch.bfloat16)
-        b2 = _synthetic((d,), 4, "bias").to(torch.bfloat16)
+        if host_tensors is not None:          # the same seeded tensors, already generated for another sharding
+            x, w1, b1, w2, b2 = host_tensors
+        else:
+            x = _synthetic((T, d), 0, "activation").to(torch.bfloat16)
+            w1 = _synthetic((d, f), 1, "weight").to(torch.bfloat16)
+            b1 = _synthetic((f,), 2, "bias").to(torch.bfloat16)
+            w2 = _synthetic((f, d), 3, "weight").to(torch.bfloat16)
+            b2 = _synthetic((d,), 4, "bias").to(torch.bfloat16)
+        self._x_full = x
+        self.host_weights = (w1, b1, w2, b2)          # full bf16 copies on the host: what bench.py's parity check reads
         if self.mode == "fsdp":
             tl, kl1, kl2 = T // world, d // world, f // world
             self.x_host = x[rank * tl:(rank + 1) * tl].contiguous().pin_memory()
@@ -608,6 +613,9 @@ class FFNBench:
         mk = lambda: [[torch.cuda.Event() for _ in range(self.e2e_chunks)] for _ in range(2)]
         self._in_ev, self._xfree_ev, self._out_ev, self._ycopied_ev = mk(), mk(), mk(), mk()
 
+    def host_tensors(self):
+        return (self._x_full,) + tuple(self.host_weights)
+
     def parallelism_name(self):
         if self.mode == "single":
             return "1 GPU"
@@ -633,11 +641,22 @@ class FFNBench:
         total, n = 0.0, 0
         prev = None
         for tag, ev in self._events:
-            if tag != "start" and prev is not None:
+            if tag in ("gemm1", "gemm2") and prev is not None:
                 total += prev.elapsed_time(ev)
                 n += 1
             prev = ev
         return total / max(n, 1), n
+
+    def kernel_parts_ms(self, steps: int):
+        """Mean device time per step of each recorded phase (gemm1, gemm2, reduce = the part of barrier + reduction that is
+        left after the last GEMM), from the same events as mean_kernel_ms."""
+        parts = {}
+        prev = None
+        for tag, ev in self._events:
+            if tag != "start" and prev is not None:
+                parts[tag] = parts.get(tag, 0.0) + prev.elapsed_time(ev)
+            prev = ev
+        return {k: v / max(steps, 1) for k, v in parts.items()}
 
     # --- end-to-end step: host x -> device -> FFN -> host y
     def step_e2e(self):
@@ -716,16 +735,24 @@ class FFNBench:
             h2d //= self.world          # each rank uploads its share of the replicated x
         return h2d, self.y_host.numel() * 2
 
-    def ncu_traffic_bytes(self):
-        """dram read+write bytes per GEMM launch from the committed ncu --set full capture, if any."""
-        path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles", "ncu_traffic.json")
-        if os.path.exists(path):
-            try:
-                with open(path) as f:
-                    return json.load(f).get("gemm_bf16_kernel_bytes_per_launch")
-            except (OSError, ValueError):
-                return None
-        return None
+
+def ncu_traffic_bytes():
+    """dram read+write bytes per GEMM launch from the committed one-GPU ncu --set full capture of the case4 shape."""
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles", "ncu_traffic.json")
+    if os.path.exists(path):
+        try:
+            with open(path) as f:
+                return json.load(f).get("gemm_bf16_kernel_bytes_per_launch")
+        except (OSError, ValueError):
+            return None
+    return None
+
+
+def ffn_algorithmic_bytes(cfg, world: int):
+    """Bytes one GEMM launch of the tensor-parallel FFN must move on ONE rank (operands read once + result written once):
+    GEMM1 x[T,d] + W1[d,f/W] + h[T,f/W]; GEMM2 h + W2[f/W,d] + y partial [T,d]; bf16."""
+    T, d, f = cfg["batch"] * cfg["seq"], cfg["d_model"], cfg["d_ff"] // world
+    return {"gemm1": 2 * (T * d + d * f + T * f), "gemm2": 2 * (T * f + f * d + T * d)}
 
 
 def attention_mesh(world: int):
@@ -733,7 +760,7 @@ def attention_mesh(world: int):
     return {1: (1, 1), 2: (1, 2), 4: (2, 2), 8: (2, 4)}.get(world, (1, world))
 
 
-def run_attention_workload(cfg, rank, world, dev, steps, warmup):
+def run_attention_workload(cfg, rank, world, dev, steps, warmup, keep=False):
     """The MHA layer of BASELINE.json's case5 / case6 configs (projections + attention core + out-projection)
     on a (data x model) mesh: batch over 'data', heads over 'model' (fused push reduce-scatter for the
     row-parallel out-projection).  Returns timing / FLOP figures (max over ranks)."""
@@ -806,8 +833,29 @@ def run_attention_workload(cfg, rank, world, dev, steps, warmup):
         ms, parts = float(t[0]), {"qkv": float(t[1]), "attn": float(t[2]), "out": float(t[3])}
     core = 2.0 * B * H * S * (S + 1) * D if causal else 4.0 * B * H * S * S * D
     proj = 8.0 * B * S * M * inner
-    return {"ms_per_step": ms, "parts_ms": parts, "core_flops": core, "proj_flops": proj, "mesh": (d_ax, m_ax),
-            "launches": int(capi.launch_count() - l0), "steps": steps}
+    res = {"ms_per_step": ms, "parts_ms": parts, "core_flops": core, "proj_flops": proj, "mesh": (d_ax, m_ax),
+           "launches": int(capi.launch_count() - l0), "steps": steps}
+    if keep:      # for bench.py's stage-wise parity check of what was just timed
+        res.update(layer=layer, x=x, group=group if m_ax > 1 else None)
+    return res
+
+
+def attention_core_sample(dev, B, S, H, D, causal, peaks, iters=5):
+    """CUDA-event timing of the attention core alone at one shape (the head dim 64 figure of the default bench line)."""
+    q, k, v = (torch.randn(B, S, H, D, device=dev).to(torch.bfloat16) for _ in range(3))
+    o = torch.empty_like(q)
+    for _ in range(2):
+        capi.attention_fwd(q, k, v, causal=causal, out=o)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        capi.attention_fwd(q, k, v, causal=causal, out=o)
+    e1.record()
+    torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1) / iters
+    flops = 2.0 * B * H * S * (S + 1) * D if causal else 4.0 * B * H * S * S * D
+    tf = flops / (ms * 1e-3) / 1e12
+    return {"shape": [B, S, H, D], "causal": causal, "ms": ms, "core_tflops": tf, "core_frac_of_peak": tf / peaks["bf16_burst"]}
 
 
 def bench_attention(args, cfg, rank, world, dev, metric, unit, peaks, sampler, attn_flops):
