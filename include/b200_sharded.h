@@ -268,6 +268,31 @@ int b200_ffn_fwd(const void* x, const void* W1, const void* b1, const void* W2, 
 int b200_ffn_fwd_static_scratch(const void* x, const void* W1, const void* b1, const void* W2, const void* b2, void* y,
                                 int y_dtype, int T, int d_model, int F, int act, void* stream);
 
+/*
+ * Random fill of ONE DEVICE'S SHARD with the values jax.random assigns to the whole array ("born sharded": no host
+ * generation, no placement copy).  key = the two uint32 words of a jax threefry key (jax.random.PRNGKey(s) = {0, s});
+ * global_shape / shard_start / shard_shape describe the row-major array and this device's slice of it (ndim <= 4);
+ * element i of the flattened global array is word i of jax's threefry2x32 bit stream for (key, size), transformed as
+ *   B200_RNG_BITS              raw uint32 words                                   (out: uint32)
+ *   B200_RNG_UNIFORM           jax.random.uniform(key, shape, minval=lo, maxval=hi)   (out: f32)
+ *   B200_RNG_NORMAL            jax.random.normal(key, shape)                      (case1a.py:16-18; case6_attention.py:152)
+ *   B200_RNG_TRUNCATED_NORMAL  jax.random.truncated_normal(key, lo, hi, shape); with lo = -2, hi = 2 and
+ *                              scale = sqrt(1 / fan_in) / 0.87962566103423978 this is nn.initializers.lecun_normal(),
+ *                              the initialiser of every Dense kernel under model.init (case6_attention.py:57,86,171-196)
+ * each multiplied by `scale` (0 is read as 1).  The integer stages are bit-exact with jax; the float stages follow the
+ * published formulas in f32 (XLA may differ by an ulp).  Arrays of 2^32 or more elements are not supported.
+ */
+typedef enum { B200_RNG_BITS = 0, B200_RNG_UNIFORM = 1, B200_RNG_NORMAL = 2, B200_RNG_TRUNCATED_NORMAL = 3 } b200_rng_distribution;
+typedef struct {
+  uint32_t key[2];
+  int ndim;
+  int64_t global_shape[4], shard_start[4], shard_shape[4];
+  int distribution;
+  float lo, hi;
+  float scale;
+} b200_random_args;
+int b200_random_fill(const b200_random_args* args, void* out, void* stream);
+
 /* dst[i] = bf16(src[i]) -- the per-call f32->bf16 parameter/activation cast flax
  * promote_dtype performs inside nn.Dense (case6_attention.py:61-90). n elements. */
 int b200_cast_f32_to_bf16(const float* src, void* dst, int64_t n, void* stream);

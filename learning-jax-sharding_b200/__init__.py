@@ -11,14 +11,14 @@ The directory is named ``learning-jax-sharding_b200``; import it as ``learning_j
     A = ljs.device_put(A, sharding.replicate(axis=0, keepdims=True))
     C = ljs.lax.dot(A, B)
 """
-from . import capi, debug, lax, nn, runtime, train  # noqa: F401
+from . import capi, debug, lax, nn, random, runtime, train  # noqa: F401
 from .array import ShardedArray, device_put, reshard  # noqa: F401
 from .runtime import get_runtime, init_distributed, init_virtual  # noqa: F401
 from .sharding import (Device, Mesh, NamedSharding, PartitionSpec, PositionalSharding,  # noqa: F401
                        ReplicatedSharding, SliceSharding, create_device_mesh, current_mesh)
 
 __all__ = [
-    "capi", "debug", "lax", "nn", "runtime", "train", "ShardedArray", "device_put", "reshard", "get_runtime", "init_distributed",
+    "capi", "debug", "lax", "nn", "random", "runtime", "train", "ShardedArray", "device_put", "reshard", "get_runtime", "init_distributed",
     "init_virtual", "Device", "Mesh", "NamedSharding", "PartitionSpec", "PositionalSharding", "ReplicatedSharding",
     "SliceSharding", "create_device_mesh", "current_mesh",
 ]

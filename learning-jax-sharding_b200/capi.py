@@ -23,6 +23,7 @@ BF16, F32 = 0, 1
 EPI_NONE, EPI_BIAS, EPI_BIAS_RELU, EPI_BIAS_GELU_TANH, EPI_RELU, EPI_GELU_TANH = range(6)
 B_KN, B_NK = 0, 1
 A_MK, A_KM = 0, 1
+RNG_BITS, RNG_UNIFORM, RNG_NORMAL, RNG_TRUNCATED_NORMAL = range(4)
 
 EXPORTED_SYMBOLS = (
     "b200_version",
@@ -62,6 +63,7 @@ EXPORTED_SYMBOLS = (
     "b200_peer_gather",
     "b200_peer_barrier",
     "b200_sum_bf16_partials",
+    "b200_random_fill",
 )
 
 
@@ -77,6 +79,13 @@ class AttentionArgs(ctypes.Structure):
                 ("lse2", ctypes.c_void_p), ("B", ctypes.c_int), ("Sq", ctypes.c_int), ("Sk", ctypes.c_int),
                 ("H", ctypes.c_int), ("D", ctypes.c_int), ("strides", ctypes.c_int64 * 12), ("scale", ctypes.c_float),
                 ("causal", ctypes.c_int), ("variant", ctypes.c_int)]
+
+
+class RandomArgs(ctypes.Structure):
+    """b200_random_args of include/b200_sharded.h."""
+    _fields_ = [("key", ctypes.c_uint32 * 2), ("ndim", ctypes.c_int), ("global_shape", ctypes.c_int64 * 4),
+                ("shard_start", ctypes.c_int64 * 4), ("shard_shape", ctypes.c_int64 * 4), ("distribution", ctypes.c_int),
+                ("lo", ctypes.c_float), ("hi", ctypes.c_float), ("scale", ctypes.c_float)]
 
 
 class GemmArgs(ctypes.Structure):
@@ -133,6 +142,7 @@ def load():
     lib.b200_sum_bf16_partials.argtypes = [vp, i64, i32, vp, i64, vp, i64, vp]
     lib.b200_gemm_f32.argtypes = [vp, i64, i64, vp, i64, i64, vp, i64, i64, i32, i32, i32, i32, i32, vp]
     lib.b200_attention_fwd.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32] + [i64] * 12 + [f32, i32, vp]
+    lib.b200_random_fill.argtypes = [ctypes.POINTER(RandomArgs), vp, vp]
     lib.b200_attention_fwd_ex.argtypes = [ctypes.POINTER(AttentionArgs), vp]
     lib.b200_ffn_fwd_static_scratch.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp]
     lib.b200_attention_fwd_lse.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32] + [i64] * 12 + [f32, i32, vp]
@@ -284,6 +294,29 @@ def adam_step(param, grad, mu, nu, *, step: int, lr=1e-3, b1=0.9, b2=0.999, eps=
                                    ctypes.c_float(eps), ctypes.c_int(step), _stream(param))
     _check(rc, "b200_adam_step")
     return param
+
+
+def random_fill(out, key, global_shape, shard_start, distribution, *, lo=0.0, hi=0.0, scale=1.0):
+    """Fill ``out`` (this device's contiguous shard: f32, or int32 for RNG_BITS) with the values jax.random gives the
+    slice [shard_start, shard_start + out.shape) of an array of ``global_shape`` under ``key`` (two uint32 words)."""
+    _require_cuda(out)
+    nd = len(global_shape)
+    if not (1 <= nd <= 4) or out.dim() != nd or len(shard_start) != nd or not out.is_contiguous():
+        raise B200Error("random_fill: out must be a contiguous tensor of the same rank (1..4) as global_shape")
+    want = torch.int32 if distribution == RNG_BITS else torch.float32
+    if out.dtype != want:
+        raise B200Error(f"random_fill: distribution {distribution} writes {want}")
+    a = RandomArgs()
+    a.key = (ctypes.c_uint32 * 2)(int(key[0]) & 0xFFFFFFFF, int(key[1]) & 0xFFFFFFFF)
+    a.ndim = nd
+    a.global_shape = (ctypes.c_int64 * 4)(*(list(global_shape) + [1] * (4 - nd)))
+    a.shard_start = (ctypes.c_int64 * 4)(*(list(shard_start) + [0] * (4 - nd)))
+    a.shard_shape = (ctypes.c_int64 * 4)(*(list(out.shape) + [1] * (4 - nd)))
+    a.distribution, a.lo, a.hi, a.scale = distribution, float(lo), float(hi), float(scale)
+    with torch.cuda.device(out.device):
+        rc = load().b200_random_fill(ctypes.byref(a), _ptr(out), _stream(out))
+    _check(rc, "b200_random_fill")
+    return out
 
 
 def gemm_f32(a, b, *, out=None, accumulate=False):

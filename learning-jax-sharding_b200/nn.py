@@ -67,8 +67,24 @@ def logical_to_mesh_axes(names: Sequence[Optional[str]], rules=None) -> Partitio
     return PartitionSpec(*out)
 
 
-def logical_to_mesh_sharding(names, mesh: Mesh, rules) -> NamedSharding:
+def logical_to_mesh_sharding(names, mesh: Mesh, rules):
+    """``nn.logical_to_mesh_sharding``: a tuple of logical names -> NamedSharding; a tree (dict / tuple of such tuples,
+    as ``get_partition_spec`` returns for a state) -> the same tree of NamedShardings (case6_attention.py:189-191)."""
+    if isinstance(names, dict):
+        return {k: logical_to_mesh_sharding(v, mesh, rules) for k, v in names.items()}
+    if isinstance(names, (tuple, list)) and names and isinstance(names[0], (tuple, list)):
+        return type(names)(logical_to_mesh_sharding(v, mesh, rules) for v in names)
     return NamedSharding(mesh, logical_to_mesh_axes(names, rules))
+
+
+def get_partition_spec(model):
+    """``nn.get_partition_spec(abstract_state)`` for this library's modules: the tree of logical axis names the module
+    attached to its parameters with ``with_logical_partitioning`` (case6_attention.py:56-59,85-88,189).  Unannotated
+    leaves (the bias) are replicated: an empty tuple."""
+    tree = {}
+    for name, axes in model.param_axes.items():
+        tree[name] = (tuple(axes), ()) if name in getattr(model, "biased", ()) else tuple(axes)
+    return tree
 
 
 def with_logical_constraint(x: ShardedArray, names: Sequence[Optional[str]]) -> ShardedArray:
@@ -265,6 +281,35 @@ class FlaxAttention:
     # logical names of the parameters (case6_attention.py:56-59,85-88)
     param_axes = {"to_q": ("embed", "heads"), "to_k": ("embed", "heads"), "to_v": ("embed", "heads"),
                   "to_out_0": ("heads", "embed")}
+    biased = ("to_out_0",)          # nn.Dense(query_dim) keeps its default use_bias=True (case6_attention.py:83-90)
+
+    def param_shapes(self):
+        inner = self.heads * self.dim_head
+        return {"to_q": (self.query_dim, inner), "to_k": (self.query_dim, inner), "to_v": (self.query_dim, inner),
+                "to_out_0": (inner, self.query_dim)}
+
+    def init(self, key, out_shardings) -> Dict[str, object]:
+        """``model.init`` under ``jit(..., out_shardings=logical_state_sharding)`` (case6_attention.py:171-196): every
+        Dense kernel is lecun_normal and comes into being ALREADY SHARDED -- each device generates exactly its slice in its
+        own memory (counter-based threefry, ``random.lecun_normal``), nothing is drawn on the host or moved afterwards;
+        the bias is zeros (flax's default bias_init).  ``out_shardings`` = ``logical_to_mesh_sharding(
+        get_partition_spec(model), mesh, rules)``; ``key`` = ``random.PRNGKey(seed)``."""
+        from . import random as _random
+        rt = _rt.get_runtime()
+        params = {}
+        for name, shape in self.param_shapes().items():
+            sh = out_shardings[name]
+            if name in self.biased:
+                k_sh, b_sh = sh
+                kernel = _random.lecun_normal(_random.path_key(key, name + "/kernel"), shape, k_sh)
+                idx = b_sh.devices_indices_map((shape[1],))
+                bias = ShardedArray((shape[1],), torch.float32, b_sh,
+                                    {d: torch.zeros(idx[d][0].stop - idx[d][0].start, dtype=torch.float32,
+                                                    device=rt.buffer_device(d)) for d in rt.local_device_ids if d in idx})
+                params[name] = (kernel, bias)
+            else:
+                params[name] = _random.lecun_normal(_random.path_key(key, name + "/kernel"), shape, sh)
+        return params
 
     def init_host(self, seed: int = 1) -> Dict[str, object]:
         """lecun-normal-like f32 parameters on the host (stand-in for model.init, case6_attention.py:171-178)."""
