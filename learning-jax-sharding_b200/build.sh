@@ -8,6 +8,8 @@ out="$here/libb200sl.so"
 NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
 FLAGS=(-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC
        --expt-relaxed-constexpr -Xptxas -v ${B200_EXTRA_NVCC_FLAGS:-})
+# --clean: forget every object file first (what __graft_entry__.build() does, so that "does it build" really compiles)
+if [[ "${1:-}" == "--clean" ]]; then rm -rf "$here/build"; fi
 mkdir -p "$here/build"
 objs=()
 pids=()
