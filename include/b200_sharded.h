@@ -139,6 +139,14 @@ typedef struct {
                                            i.e. the product is (stored A)^T . B -- the weight-gradient GEMM dW = x^T . dy of
                                            jax.grad through nn.Dense (case5_attention_dense.py:130-139) */
   b200_gemm_tuning tune;                /* per-call overrides of the launch heuristics; all zero = library choice */
+  int a_blocks_inner, a_outer_stride;   /* two-level row-blocked A view (0 = off): block q of a_rows_per_block rows starts
+                                           at row (q % a_blocks_inner) * a_block_stride + (q / a_blocks_inner) *
+                                           a_outer_stride.  With a [batch, seq, K] activation, a_rows_per_block = seq / W,
+                                           a_blocks_inner = batch, a_block_stride = seq, a_outer_stride = seq / W the
+                                           product comes out in "owner j: its seq block of every batch item" order, which
+                                           together with the row-block scatter (m_rows_per_block = batch * seq / W) is the
+                                           reduce-scatter ALONG SEQ that out_shardings = P('data','model') asks for
+                                           (case6_attention.py:161,230), whatever the batch size */
 } b200_gemm_args;
 int b200_gemm_bf16_ex(const b200_gemm_args* args, void* stream);
 

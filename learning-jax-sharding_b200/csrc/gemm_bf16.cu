@@ -49,6 +49,10 @@ struct GemmParams {
   // optional row-blocked view of A: logical row m lives at physical row
   // (m / a_rows_per_block) * a_block_stride + m % a_rows_per_block   (0 = plain row-major)
   int a_rows_per_block, a_block_stride;
+  // two-level form of that view (a_blocks_inner > 0): block q of a_rows_per_block rows starts at physical row
+  // (q % a_blocks_inner) * a_block_stride + (q / a_blocks_inner) * a_outer_stride -- "sequence block j of every batch
+  // item, owner by owner": the row order in which a [batch, seq]-shaped activation is reduce-scattered along seq
+  int a_blocks_inner, a_outer_stride;
   int group_m;   // tile rasterisation: group_m row-blocks sweep all column-blocks together (L2 reuse)
   // optional row-block scatter of the OUTPUT (fused reduce-scatter push): logical row m belongs to row block
   // (m / m_rows_per_block + m_block_rot) % m_num_blocks; A is read from that physical block and C is written
@@ -158,7 +162,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       if (p.m_rows_per_block > 0)
         m0 = ((m0 / p.m_rows_per_block + p.m_block_rot) % p.m_num_blocks) * p.m_rows_per_block +
              m0 % p.m_rows_per_block;
-      if (p.a_rows_per_block > 0) m0 = (m0 / p.a_rows_per_block) * p.a_block_stride + m0 % p.a_rows_per_block;
+      if (p.a_rows_per_block > 0) {
+        const int q = m0 / p.a_rows_per_block, r = m0 % p.a_rows_per_block;
+        m0 = p.a_blocks_inner > 0
+                 ? (q % p.a_blocks_inner) * p.a_block_stride + (q / p.a_blocks_inner) * p.a_outer_stride + r
+                 : q * p.a_block_stride + r;
+      }
       const int n0 = n_blk * BN + cta_rank * Cfg::kBNcta;
       for (int kb = 0; kb < num_kb; ++kb) {
         mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -423,9 +432,14 @@ static int launch_gemm(const void* A, int64_t lda, const void* B, int64_t ldb, c
   CUtensorMap tmA, tmB;
   {
     uint64_t a_rows = static_cast<uint64_t>(p.M);
-    if (p.a_rows_per_block > 0)
-      a_rows = static_cast<uint64_t>((p.M + p.a_rows_per_block - 1) / p.a_rows_per_block - 1) * p.a_block_stride +
-               p.a_rows_per_block;
+    if (p.a_rows_per_block > 0) {
+      const uint64_t nblk = static_cast<uint64_t>((p.M + p.a_rows_per_block - 1) / p.a_rows_per_block);
+      if (p.a_blocks_inner > 0)
+        a_rows = static_cast<uint64_t>(p.a_blocks_inner - 1) * p.a_block_stride +
+                 (nblk / p.a_blocks_inner - 1) * p.a_outer_stride + p.a_rows_per_block;
+      else
+        a_rows = (nblk - 1) * p.a_block_stride + p.a_rows_per_block;
+    }
     uint64_t dims[2] = {static_cast<uint64_t>(p.K), a_rows};
     uint64_t strides[2] = {0, static_cast<uint64_t>(lda) * 2};
     uint32_t box[2] = {kBK, kBM};
@@ -535,11 +549,19 @@ extern "C" int b200_gemm_bf16_ex(const b200_gemm_args* args, void* stream) {
     B200_REQUIRE(args->m_rows_per_block % 256 == 0 && M % args->m_rows_per_block == 0,
                  "b200_gemm_bf16: m_rows_per_block must be a multiple of 256 that divides M");
     B200_REQUIRE(out_dtype == B200_BF16, "b200_gemm_bf16: row-block scatter writes bf16 only");
-    B200_REQUIRE(a_rows_per_block == 0 || a_rows_per_block == args->m_rows_per_block,
-                 "b200_gemm_bf16: with the row-block scatter, a_rows_per_block must be 0 or equal m_rows_per_block");
+    B200_REQUIRE(a_rows_per_block == 0 || a_rows_per_block == args->m_rows_per_block ||
+                     (args->a_blocks_inner > 0 && args->m_rows_per_block == a_rows_per_block * args->a_blocks_inner),
+                 "b200_gemm_bf16: with the row-block scatter, a_rows_per_block must be 0, equal m_rows_per_block, or "
+                 "(two-level view) m_rows_per_block / a_blocks_inner");
   } else {
     B200_REQUIRE(!scatter, "b200_gemm_bf16: c_block_ptrs needs m_rows_per_block");
   }
+  B200_REQUIRE(args->a_blocks_inner >= 0 && args->a_outer_stride >= 0, "b200_gemm_bf16: negative two-level view parameters");
+  if (args->a_blocks_inner > 0)
+    B200_REQUIRE(a_rows_per_block > 0 && M % (a_rows_per_block * args->a_blocks_inner) == 0 &&
+                     args->a_outer_stride >= a_rows_per_block,
+                 "b200_gemm_bf16: the two-level A view needs a_rows_per_block > 0, M a multiple of a_rows_per_block * "
+                 "a_blocks_inner and a_outer_stride >= a_rows_per_block");
   B200_REQUIRE(M > 0 && N > 0 && K > 0, "b200_gemm_bf16: M, N, K must be positive (got %d, %d, %d)", M, N, K);
   B200_REQUIRE(K % 8 == 0 && N % 8 == 0, "b200_gemm_bf16: K and N must be multiples of 8 (got K=%d N=%d)", K, N);
   B200_REQUIRE(b_layout == B200_B_KN || b_layout == B200_B_NK, "b200_gemm_bf16: bad b_layout %d", b_layout);
@@ -571,6 +593,8 @@ extern "C" int b200_gemm_bf16_ex(const b200_gemm_args* args, void* stream) {
   p.out_f32 = out_dtype == B200_F32;
   p.a_rows_per_block = a_rows_per_block;
   p.a_block_stride = a_block_stride;
+  p.a_blocks_inner = args->a_blocks_inner;
+  p.a_outer_stride = args->a_outer_stride;
   p.c_block_ptrs = args->c_block_ptrs;
   p.m_rows_per_block = args->m_rows_per_block;
   p.m_block_rot = args->m_block_rot;

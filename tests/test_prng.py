@@ -94,7 +94,11 @@ def test_kernel_known_answers(ljs):
     ljs.init_virtual(1, "cuda:0")
     r = ljs.random
     key = r.PRNGKey(0)
-    assert r.bits(key, (2,)).device_buffers[0].cpu().numpy().view(np.uint32).tolist() == [0x6b200159, 0x99ba4efe]
+    # one word: the count vector [0] is padded to [0, 0], so the block is threefry(key = (0, 0), counter = (0, 0))
+    assert r.bits(key, (1,)).device_buffers[0].cpu().numpy().view(np.uint32).tolist() == [0x6b200159]
+    # four words: split(PRNGKey(0)) as documented
+    assert r.bits(key, (4,)).device_buffers[0].cpu().numpy().view(np.uint32).tolist() == [4146024105, 967050713, 2718843009,
+                                                                                         1272950319]
     assert abs(float(r.uniform(key, (1,)).device_buffers[0].cpu()) - 0.41845703) < 5e-9
     assert abs(float(r.normal(key, (1,)).device_buffers[0].cpu()) - (-0.20584226)) < 2e-8
     np.testing.assert_allclose(r.normal(key, (3,)).device_buffers[0].cpu().numpy(), [1.8160863, -0.48262316, 0.33988908],
