@@ -306,7 +306,8 @@ def attention_parity_check(r, cfg, dist, dev, rank, world):
     # every rank of the model group evaluates the partial of EVERY member's sampled rows (8 x m_ax rows): tiny
     parts = []
     for owner in range(m_ax):
-        o_rows = layer.o[(owner * blk + yrows).to(dev)].cpu().float()
+        grows = layer.rs.global_rows(yrows, owner) if layer.rs is not None else yrows
+        o_rows = layer.o[grows.to(dev)].cpu().float()
         parts.append(o_rows @ layer.wo.cpu().float())
     mine = torch.stack(parts)                                            # [m_ax, 8, M] f32: this rank's partial products
     if m_ax > 1:

@@ -117,20 +117,35 @@ class PeerReduceScatter:
     pushed as two GEMM launches, each covering HALF of every owner's row block, and the barrier + reduction
     of the first half run on a side stream underneath the second GEMM, so only half of the reduction (and one
     barrier) is left after the last GEMM tile.  The side stream is joined before `finish` returns: from outside
-    the call stays ordered on the caller's stream."""
+    the call stays ordered on the caller's stream.
+
+    `batch` > 1: the T rows are a [batch, seq] activation and the result is scattered ALONG SEQ -- owner j receives
+    rows (b, j*seq/W + s') for every batch item b, laid out [batch, seq/W, N]: the sequence-sharded out_shardings
+    P('data','model') of the reference (case6_attention.py:161,230).  The GEMM reads its A operand through the
+    two-level row-blocked view (b200_gemm_args.a_blocks_inner); chunks then split the batch items.  `batch` = 1
+    scatters contiguous blocks of the flattened rows."""
 
     _FLAG_BYTES = 1024
 
-    def __init__(self, T: int, N: int, group, device, chunks: int = 2):
+    def __init__(self, T: int, N: int, group, device, chunks: int = 2, batch: int = 1):
         import torch.distributed as dist
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         W = self.world
         if T % W or (T // W) % 256:
             raise ValueError(f"T={T} must split into {W} blocks of a multiple of 256 rows")
         self.T, self.N, self.R = T, N, T // W
+        self.batch = batch
         chunks = int(os.environ.get("B200_TP_CHUNKS", chunks))
-        while chunks > 1 and (self.R % chunks or (self.R // chunks) % 256):
-            chunks -= 1
+        if batch > 1:
+            self.seq = T // batch
+            self.rpb = self.seq // W                             # rows of one (batch item, owner) cell
+            if T % batch or self.seq % W or self.rpb % 128:
+                raise ValueError(f"seq={T // batch} must split into {W} blocks of a multiple of 128 rows")
+            while chunks > 1 and (batch % chunks or ((batch // chunks) * self.rpb) % 256):
+                chunks -= 1
+        else:
+            while chunks > 1 and (self.R % chunks or (self.R // chunks) % 256):
+                chunks -= 1
         self.chunks = max(chunks, 1)
         self.Rc = self.R // self.chunks                         # rows of one chunk inside one owner's block
         self.slot = self.R * N                                  # elements of one receive slot
@@ -158,8 +173,19 @@ class PeerReduceScatter:
         self.reduced = torch.cuda.Event()
         dist.barrier(group=group)
 
+    def global_rows(self, local_rows: torch.Tensor, owner: int) -> torch.Tensor:
+        """Rows of the flattened [T, .] input that the given rows of `owner`'s output block correspond to."""
+        if self.batch > 1:
+            return (local_rows // self.rpb) * self.seq + owner * self.rpb + local_rows % self.rpb
+        return owner * self.R + local_rows
+
     def _push(self, a: torch.Tensor, w: torch.Tensor, c: int):
-        if self.chunks == 1:
+        if self.batch > 1:
+            inner = self.batch // self.chunks                   # batch items of this launch
+            capi.gemm_bf16_scatter(a[c * inner * self.seq:], w, self.c_ptrs[self.buf][c], self.Rc,
+                                   (self.rank + 1) % self.world, self.N, M=self.world * self.Rc,
+                                   a_view=(self.rpb, inner, self.seq, self.rpb))
+        elif self.chunks == 1:
             capi.gemm_bf16_scatter(a, w, self.c_ptrs[self.buf][0], self.R, (self.rank + 1) % self.world, self.N)
         else:
             # logical block j of this launch = rows [c*Rc, (c+1)*Rc) of owner j's row block of `a`
@@ -220,15 +246,16 @@ class FusedTensorParallelFFN:
     flag barrier and one local pass summing the W received bf16 partials in f32 (+ b2).  No NCCL on the
     data path; the first GEMM runs at full size, the second as two launches (half of every owner's block each)
     so that the barrier + reduction of the first half hide under the second (PeerReduceScatter).  Same result layout as
-    TensorParallelFFN: this rank's sequence block y[rank*T/W : (rank+1)*T/W]."""
+    TensorParallelFFN: this rank's sequence block y[rank*T/W : (rank+1)*T/W]; with `batch` > 1 the block of every batch
+    item along seq, [batch, seq/W, d_model] (PeerReduceScatter)."""
 
-    def __init__(self, w1, b1, w2, b2, act: str, T: int, group, chunks: int = 2):
+    def __init__(self, w1, b1, w2, b2, act: str, T: int, group, chunks: int = 2, batch: int = 1):
         self.w1, self.b1, self.w2, self.b2 = w1, b1, w2, b2
         self.act = _act_code(act, b1 is not None)
         self.d_model, self.F = w1.shape
         self.T = T
         dev = w1.device
-        self.rs = PeerReduceScatter(T, self.d_model, group, dev, chunks=chunks)
+        self.rs = PeerReduceScatter(T, self.d_model, group, dev, chunks=chunks, batch=batch)
         self.world, self.rank = self.rs.world, self.rs.rank
         self.h = torch.empty((T, self.F), dtype=torch.bfloat16, device=dev)
         self.y = torch.empty((self.rs.R, self.d_model), dtype=torch.bfloat16, device=dev)
@@ -247,10 +274,11 @@ class ShardedMHA:
     over the `group` ranks (the BASELINE.json case6 layout): to_q/to_k/to_v column-parallel
     and fused into ONE [M, 3*Hl*D] GEMM, attention on the local heads straight out of that buffer (strided
     q/k/v views, no transpose), to_out_0 row-parallel with the fused push reduce-scatter (or a plain GEMM +
-    bias on one GPU).  x: [B, S, M] bf16 replicated over the group; returns this rank's sequence block of y
-    flattened to [B*S/W, M]."""
+    bias on one GPU).  x: [B, S, M] bf16 replicated over the group; returns this rank's sequence block of y,
+    [B, S/W, M] flattened to [B*S/W, M]."""
 
-    def __init__(self, wq, wk, wv, wo, bo, heads_local: int, dim_head: int, B: int, S: int, causal: bool, group=None):
+    def __init__(self, wq, wk, wv, wo, bo, heads_local: int, dim_head: int, B: int, S: int, causal: bool, group=None,
+                 scatter: str = "seq"):
         self.Hl, self.D, self.B, self.S, self.causal = heads_local, dim_head, B, S, causal
         self.wqkv = torch.cat([wq, wk, wv], dim=1).contiguous()        # [M, 3*Hl*D]
         self.wo, self.bo = wo, bo
@@ -266,7 +294,9 @@ class ShardedMHA:
             import torch.distributed as dist
             self.world = dist.get_world_size(group)
         if self.world > 1:
-            self.rs = PeerReduceScatter(T, self.M, group, dev)
+            # scatter = "seq": y is this rank's block along S of every batch item, [B, S/W, M] -- the out_shardings
+            # P('data','model') of case6_attention.py:230; "rows": a contiguous block of the flattened B*S rows
+            self.rs = PeerReduceScatter(T, self.M, group, dev, batch=B if scatter == "seq" else 1)
             self.y = torch.empty((self.rs.R, self.M), dtype=torch.bfloat16, device=dev)
         else:
             self.y = torch.empty((T, self.M), dtype=torch.bfloat16, device=dev)

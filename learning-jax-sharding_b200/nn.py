@@ -244,13 +244,97 @@ def dot_product_attention(q: ShardedArray, k: ShardedArray, v: ShardedArray, *, 
     return ShardedArray(q.shape, torch.bfloat16, q.sharding, out)
 
 
+# ------------------------------------------------------------------- fused fast paths (one process per GPU)
+# The generic plans above are what runs on a virtual mesh and under gloo.  On real GPUs (DistributedRuntime over NCCL) the
+# same calls, with the same operand shardings, are served by the resident fused layers of layers.py -- peer-memory
+# reduce-scatter fused into the row-parallel GEMM, bf16 weight copies made once, output buffers reused -- so that the
+# reference-shaped API IS the throughput path.  A layer object is cached per (parameter arrays, activation shape); the
+# cache keeps the parameter arrays alive, and `invalidate_fast_layers()` drops it (train steps that update f32 master
+# parameters in place call it, because the layers hold bf16 copies of those).
+_fast_layers: Dict[tuple, object] = {}
+
+
+def invalidate_fast_layers():
+    _fast_layers.clear()
+
+
+def _model_group(rt, mesh, axis):
+    """(ranks, process group) of the ranks that differ from this one only along `axis`; collective over the job."""
+    return rt._my_group(mesh.axis_groups((axis,)))
+
+
+def _fast_ffn(x, w1, b1, w2, b2, act, scatter_dim):
+    rt = _rt.get_runtime()
+    if getattr(rt, "kind", "") != "distributed" or not rt.on_cuda or scatter_dim is None or _rt._compute_override is not None:
+        return None
+    if not all(isinstance(t.sharding, NamedSharding) for t in (x, w1, w2)):
+        return None
+    mesh = x.sharding.mesh
+    xa = _axes(x)
+    (k1, n1), (k2, n2) = _axes(w1), _axes(w2)
+    if k1 or n2 or len(n1) != 1 or tuple(k2) != tuple(n1) or xa[-1]:
+        return None                                   # not the column-parallel -> row-parallel pattern
+    m = n1[0]
+    W = mesh.axis_size(m)
+    if W == 1 or any(m in r for r in xa) or x.ndim not in (2, 3) or scatter_dim >= x.ndim - 1:
+        return None                                   # x must be replicated over the model axis
+    xs = x.shard(rt.rank)
+    lead = tuple(xs.shape[:-1])
+    T = 1
+    for v in lead:
+        T *= v
+    d = xs.shape[-1]
+    if x.ndim == 3 and scatter_dim == 1:
+        batch = lead[0]
+        if lead[1] % W or (lead[1] // W) % 128:
+            return None
+        out_local = (lead[0], lead[1] // W, d)
+    else:                                             # leading dim: contiguous blocks of the flattened rows
+        batch = 1
+        if lead[0] % W:
+            return None
+        out_local = (lead[0] // W,) + lead[1:] + (d,)
+    if T % (W * 256):
+        return None
+    key = ("ffn", id(w1), id(b1), id(w2), id(b2), lead, act, scatter_dim)
+    entry = _fast_layers.get(key)
+    if entry is None:
+        from . import layers
+        ranks, pg = _model_group(rt, mesh, m)
+        if b1 is not None:
+            b1 = reshard(b1, NamedSharding(mesh, PartitionSpec(m)))
+        if b2 is not None and not b2.sharding.is_fully_replicated(b2.shape):
+            b2 = reshard(b2, NamedSharding(mesh, PartitionSpec()))
+        bf = lambda t: None if t is None else _to_bf16(t.shard(rt.rank)).contiguous()
+        try:
+            layer = layers.FusedTensorParallelFFN(bf(w1), bf(b1), bf(w2), bf(b2), act, T, pg, batch=batch)
+        except Exception:       # noqa: BLE001 - e.g. CUDA IPC not permitted: the generic plan still works
+            _fast_layers[key] = False
+            return None
+        entry = _fast_layers[key] = (layer, (w1, b1, w2, b2))      # the tuple keeps the ids above valid
+    if entry is False:
+        return None
+    layer = entry[0]
+    y = layer.forward(_to_bf16(xs.reshape(T, d)))
+    rows = [tuple(r) for r in xa[:-1]]
+    rows[scatter_dim] = rows[scatter_dim] + (m,)
+    return ShardedArray(x.shape, torch.bfloat16, NamedSharding(mesh, _spec(rows + [()])), {rt.rank: y.view(out_local)})
+
+
 # ------------------------------------------------------------------------------------ FFN
 def ffn(x: ShardedArray, w1: ShardedArray, b1: Optional[ShardedArray], w2: ShardedArray, b2: Optional[ShardedArray], *,
         act: str = "gelu_tanh", scatter_dim: Optional[int] = None) -> ShardedArray:
     """y = act(x.W1 + b1).W2 + b2 (case6_attention.py:36-40).  With W1 ``P(None,'model')`` and W2
     ``P('model',None)`` this is the column-parallel -> activation -> row-parallel block: one
     all-reduce (or reduce-scatter with ``scatter_dim``) over 'model' at the end.  With W1/W2
-    ``P('data',None)`` the weights are all-gathered first (FSDP)."""
+    ``P('data',None)`` the weights are all-gathered first (FSDP).
+
+    One process per GPU, W1 / W2 sharded as above, x replicated over 'model' and ``scatter_dim`` given: the call is served by
+    ``layers.FusedTensorParallelFFN`` (reduce-scatter fused into the second GEMM over NVLink peer memory); the returned
+    array then aliases the layer's output buffer, which the next call with the same parameters overwrites."""
+    fast = _fast_ffn(x, w1, b1, w2, b2, act, scatter_dim)
+    if fast is not None:
+        return fast
     h = dense(x, w1, b1, epilogue=act)
     return dense(h, w2, b2, scatter_dim=scatter_dim)
 
@@ -334,10 +418,56 @@ class FlaxAttention:
                 out[name] = device_put(value, sh)
         return out
 
+    def _fast_heads(self, params, x: ShardedArray):
+        """layout="heads" on real GPUs: fused q/k/v projection, attention on this rank's heads, row-parallel out-projection
+        with the fused reduce-scatter along S (layers.ShardedMHA); None when the shardings are not the head-sharded set."""
+        rt = _rt.get_runtime()
+        if getattr(rt, "kind", "") != "distributed" or not rt.on_cuda or _rt._compute_override is not None or x.ndim != 3:
+            return None
+        mesh = x.sharding.mesh
+        w_o, b_o = params["to_out_0"]
+        kq, nq = _axes(params["to_q"])
+        ko, no = _axes(w_o)
+        if kq or no or len(nq) != 1 or tuple(ko) != tuple(nq) or any(_axes(params[n]) != (kq, nq) for n in ("to_k", "to_v")):
+            return None
+        m = nq[0]
+        W = mesh.axis_size(m)
+        xa = _axes(x)
+        if W == 1 or self.heads % W or xa[2] or any(m in r for r in xa):
+            return None
+        xs = x.shard(rt.rank)
+        Bl, S, M = xs.shape
+        if S % W or (S // W) % 128 or (Bl * S) % (W * 256):
+            return None
+        key = ("mha", id(params["to_q"]), id(params["to_k"]), id(params["to_v"]), id(w_o), id(b_o), (Bl, S), self.causal)
+        entry = _fast_layers.get(key)
+        if entry is None:
+            from . import layers
+            ranks, pg = _model_group(rt, mesh, m)
+            if not b_o.sharding.is_fully_replicated(b_o.shape):
+                b_o = reshard(b_o, NamedSharding(mesh, PartitionSpec()))
+            bf = lambda t: _to_bf16(t.shard(rt.rank)).contiguous()
+            try:
+                layer = layers.ShardedMHA(bf(params["to_q"]), bf(params["to_k"]), bf(params["to_v"]), bf(w_o), bf(b_o),
+                                          self.heads // W, self.dim_head, Bl, S, self.causal, pg, scatter="seq")
+            except Exception:   # noqa: BLE001
+                _fast_layers[key] = False
+                return None
+            entry = _fast_layers[key] = (layer, params)
+        if entry is False:
+            return None
+        y = entry[0].forward(_to_bf16(xs))
+        spec = _spec([tuple(xa[0]), tuple(xa[1]) + (m,), ()])
+        return ShardedArray(x.shape[:-1] + (self.query_dim,), torch.bfloat16, NamedSharding(mesh, spec),
+                            {rt.rank: y.view(Bl, S // W, self.query_dim)})
+
     def __call__(self, params, hidden_states: ShardedArray) -> ShardedArray:
         x = hidden_states
         if self.layout == "heads":
             x = with_logical_constraint(x, ("batch", None, None))          # gather the sequence on entry
+            fast = self._fast_heads(params, x)
+            if fast is not None:
+                return fast
         q = dense(x, params["to_q"])                                        # :96
         k = dense(x, params["to_k"])                                        # :98
         v = dense(x, params["to_v"])                                        # :99

@@ -72,6 +72,8 @@ class TrainState:
                 if d in p.local_shards:
                     comp.adam_step(p.shard(d), g.shard(d).contiguous(), self.mu[name].shard(d), self.nu[name].shard(d),
                                    step=step, lr=self.tx.learning_rate, b1=self.tx.b1, b2=self.tx.b2, eps=self.tx.eps)
+        from . import nn as _nn
+        _nn.invalidate_fast_layers()      # the fused layers hold bf16 copies of the f32 parameters just updated in place
         return TrainState(step, self.apply_fn, self.params, self.tx, self.mu, self.nu)
 
 

@@ -65,6 +65,20 @@ def main():
     print(f"[rank {rank}] fused TP chunks=1 vs chunks={fused.rs.chunks}: {'identical' if good else 'DIFFERENT'}", flush=True)
     ok &= good
     del fused1
+    # scatter along seq of a [batch, seq] activation (two-level A view): [4, T/4/W, d] per rank, chunks over batch items
+    fused_s = layers.FusedTensorParallelFFN(bf(w1[:, rank * fl:(rank + 1) * fl].contiguous()), bf(b1[rank * fl:(rank + 1) * fl]),
+                                            bf(w2[rank * fl:(rank + 1) * fl].contiguous()), bf(b2), "gelu_tanh", T,
+                                            dist.group.WORLD, batch=4)
+    for it in range(3):
+        ys = fused_s.forward(bf(x))
+    torch.cuda.synchronize()
+    ref = want[fused_s.rs.global_rows(torch.arange(T // world), rank)]
+    err = (ys.cpu().float() - ref).abs()
+    good = bool((err <= 2e-2 * ref.abs() + 2e-2).all())
+    print(f"[rank {rank}] fused TP, scatter along seq of [4, {T // 4}] ({fused_s.rs.chunks} chunk(s)): max_abs={err.max().item():.3e} "
+          f"{'OK' if good else 'FAIL'}", flush=True)
+    ok &= good
+    del fused_s
     # head-sharded MHA layer: fused qkv GEMM, local-head attention, row-parallel out-projection with the push reduce-scatter
     Bm, Sm, Mm, Hm, Dm = 2, 1024, 512, 8, 64
     xm = rm.synthetic((Bm, Sm, Mm), 20)
@@ -81,7 +95,7 @@ def main():
         ym = mha.forward(bf(xm))
     torch.cuda.synchronize()
     blk = Bm * Sm // world
-    ref = want_m[rank * blk:(rank + 1) * blk]
+    ref = want_m[mha.rs.global_rows(torch.arange(blk), rank)]          # this rank's block along S of every batch item
     err = (ym.cpu().float() - ref).abs()
     good = bool((err <= 2e-2 * ref.abs() + 2e-2).all())
     print(f"[rank {rank}] head-sharded MHA (causal): max_abs={err.max().item():.3e} {'OK' if good else 'FAIL'}", flush=True)
@@ -118,8 +132,71 @@ def main():
     got = y.device_buffers[0].cpu().float()
     ref = want.reshape(4, T // 4, d)[:, rank * blk:(rank + 1) * blk]
     good = bool(((got - ref).abs() <= 2e-2 * ref.abs() + 2e-2).all())
-    print(f"[rank {rank}] nn.ffn (NamedSharding, NCCL reduce-scatter): {'OK' if good else 'FAIL'}", flush=True)
+    fast_used = any(k[0] == "ffn" and v is not False for k, v in ljs.nn._fast_layers.items())
+    print(f"[rank {rank}] nn.ffn (NamedSharding, scatter_dim=1; fused fast path used: {fast_used}): {'OK' if good else 'FAIL'}",
+          flush=True)
+    ok &= good and fast_used
+    # ... and the same call through jit(apply_fn, in_shardings, out_shardings), twice (cached layer, reused buffers)
+    params_ffn = (ljs.device_put(w1, ns(P(None, "model"))), ljs.device_put(b1, ns(P("model"))),
+                  ljs.device_put(w2, ns(P("model", None))), ljs.device_put(b2, ns(P())))
+    apply_fn = ljs.nn.jit(lambda prm, xx: ljs.nn.ffn(xx, *prm, scatter_dim=1), in_shardings=(None, ns(P("data"))),
+                          out_shardings=ns(P("data", "model")))
+    xin = ljs.device_put(x.reshape(4, T // 4, d), ns(P("data")))
+    for it in range(2):
+        y = apply_fn(params_ffn, xin)
+    torch.cuda.synchronize()
+    good = bool(((y.device_buffers[0].cpu().float() - ref).abs() <= 2e-2 * ref.abs() + 2e-2).all())
+    print(f"[rank {rank}] nn.jit(apply_fn) FFN: {'OK' if good else 'FAIL'}", flush=True)
     ok &= good
+    # the attention module through the reference-shaped API on real devices (case6_attention.py:229-237): the head-sharded
+    # annotation set (fused fast path: layers.ShardedMHA, reduce-scatter along S) and the LITERAL annotation set (generic
+    # plans over NCCL: weight all-gather, K / V all-gather along S, all-to-all M -> S)
+    d_ax = 2 if world >= 4 else 1
+    mesh6 = ljs.Mesh(ljs.create_device_mesh((d_ax, world // d_ax)), ("data", "model"))
+    x6_host = rm.synthetic((4, 1024, 512), 30)
+    p6 = {"to_q": rm.synthetic((512, 512), 31, "weight"), "to_k": rm.synthetic((512, 512), 32, "weight"),
+          "to_v": rm.synthetic((512, 512), 33, "weight"),
+          "to_out_0": (rm.synthetic((512, 512), 34, "weight"), rm.synthetic((512,), 35, "bias"))}
+    want6 = rm.mha_forward(x6_host, p6, 8, 64).float()
+    x_sh = ljs.NamedSharding(mesh6, P("data", "model"))
+    x6 = ljs.device_put(x6_host, x_sh)
+    for layout, rules in (("heads", (("batch", "data"), ("heads", "model"), ("hidden", "model"))),
+                          ("literal", (("batch", "data"), ("embed", "model"), ("hidden", "model")))):
+        model = ljs.nn.FlaxAttention(512, heads=8, dim_head=64, layout=layout)
+        prm = model.shard_params(p6, mesh6, rules)
+        fn = ljs.nn.jit(lambda pp, xx: model(pp, xx), in_shardings=(None, x_sh), out_shardings=x_sh)
+        n_before = len(ljs.nn._fast_layers)
+        with mesh6, ljs.nn.axis_rules(rules):
+            for it in range(2):
+                y6 = fn(prm, x6)
+        torch.cuda.synchronize()
+        sh = y6.addressable_shards[0]
+        got6, ref6 = sh.data.cpu().float(), want6[sh.index]
+        good = bool(((got6 - ref6).abs() <= 2e-2 * ref6.abs() + 2e-2).all())
+        fast = len(ljs.nn._fast_layers) > n_before
+        print(f"[rank {rank}] FlaxAttention layout={layout} on mesh {d_ax}x{world // d_ax} via nn.jit (fused layer: {fast}): "
+              f"max_abs={(got6 - ref6).abs().max().item():.3e} {'OK' if good else 'FAIL'}", flush=True)
+        ok &= good and (fast or layout == "literal")
+    # the sharded fp32 lax.dot of case1a/1b/2/3/4 on real devices: the literal 2x4 PositionalSharding layouts need 8 GPUs;
+    # at any size the 1-D mesh form of BASELINE.json configs[0]
+    gA = torch.Generator().manual_seed(0)
+    A4, B4 = torch.randn(4, 16, generator=gA), torch.randn(16, 4, generator=gA)
+    want4 = rm.dot_f32(A4, B4)
+    lay = {}
+    if world == 8:
+        s8 = ljs.PositionalSharding(ljs.create_device_mesh((2, 4)))
+        lay = {"case1a": (s8.replicate(axis=0, keepdims=True), s8.reshape(4, 2).replicate(axis=1, keepdims=True)),
+               "case1b": (s8.replicate(axis=0, keepdims=True), s8.replicate(axis=1, keepdims=True)),
+               "case2": (s8, s8.replicate(axis=1, keepdims=True)), "case3": (s8, s8),
+               "case4": (s8.replicate(axis=1, keepdims=True), s8.replicate(axis=0, keepdims=True))}
+    m1 = ljs.Mesh(ljs.create_device_mesh((world,)), ("m",))
+    lay["mesh_1d"] = (ljs.NamedSharding(m1, P(None, "m")), ljs.NamedSharding(m1, P("m", None)))
+    for name, (sa, sb) in lay.items():
+        C4 = ljs.lax.dot(ljs.device_put(A4, sa), ljs.device_put(B4, sb))
+        good = all(bool(torch.allclose(s.data.cpu(), want4[s.index], rtol=1e-5, atol=1e-6)) for s in C4.addressable_shards)
+        print(f"[rank {rank}] lax.dot {name} on {world} GPUs: shard {tuple(C4.addressable_shards[0].data.shape)} "
+              f"{'OK' if good else 'FAIL'}", flush=True)
+        ok &= good
     # the C-ABI mesh communicators (b200_mesh_* / b200_all_reduce ...): every collective on every axis of a (2, world/2)
     # mesh (or a 1-D mesh) against values computed locally (every rank can reconstruct the others' inputs)
     uid = [ljs.capi.comm_unique_id() if rank == 0 else None]
