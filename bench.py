@@ -403,6 +403,60 @@ def sustained_leg(bench, dist, dev, local_rank, total_flops, peaks, seconds=2.5)
             "per_gpu_frac_of_burst_peak": val / bench.world / peaks["bf16_burst"], "clocks": clocks}
 
 
+def api_leg(ljs, host_tensors, cfg, act, dist, dev, rank, world, total_flops, layers_value, steps=20):
+    """The same FFN step through the reference-shaped public API: nn.jit(apply_fn, in_shardings, out_shardings) around
+    nn.ffn on NamedSharding operands of a (1, N) data x model mesh -- W1 P(None,'model'), b1 P('model'), W2 P('model',None),
+    x replicated over 'model', y left sequence-sharded P('data','model') like the scripts' out_shardings
+    (case6_attention.py:229-232).  On N > 1 GPUs nn.ffn dispatches to the fused tensor-parallel layer."""
+    from oracle import reference_math as rm
+    if world == 1:
+        ljs.init_virtual(1, str(dev))
+    P = ljs.PartitionSpec
+    mesh = ljs.Mesh(ljs.create_device_mesh((1, world)), ("data", "model"))
+    ns = lambda spec: ljs.NamedSharding(mesh, spec)
+    m = "model" if world > 1 else None
+    x, w1, b1, w2, b2 = host_tensors
+    B, S, d = cfg["batch"], cfg["seq"], cfg["d_model"]
+    params = (ljs.device_put(w1, ns(P(None, m))), ljs.device_put(b1, ns(P(m))), ljs.device_put(w2, ns(P(m, None))),
+              ljs.device_put(b2, ns(P())))
+    xin = ljs.device_put(x.reshape(B, S, d), ns(P("data")))
+    out_sh = ns(P("data", m))
+    apply_fn = ljs.nn.jit(lambda prm, xx: ljs.nn.ffn(xx, *prm, act=act, scatter_dim=1 if world > 1 else None),
+                          in_shardings=(None, ns(P("data"))), out_shardings=out_sh)
+    for _ in range(3):
+        y = apply_fn(params, xin)
+    torch.cuda.synchronize(dev)
+    if dist is not None:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        y = apply_fn(params, xin)
+    e1.record()
+    torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1) / steps
+    if dist is not None:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    # parity of what the public call returned: 8 rows of this rank's shard against the oracle
+    sh = y.addressable_shards[0]
+    yl = sh.data.reshape(-1, d)
+    rows_b = torch.randint(0, sh.data.shape[0], (8,), generator=torch.Generator().manual_seed(4000 + rank))
+    rows_s = torch.randint(0, sh.data.shape[1], (8,), generator=torch.Generator().manual_seed(5000 + rank))
+    grow = (sh.index[0].start + rows_b) * S + sh.index[1].start + rows_s
+    torch.set_num_threads(max(1, (os.cpu_count() or 1) // max(world, 1)))
+    want = rm.ffn_forward(x[grow].float(), w1.float(), b1.float(), w2.float(), b2.float(), act)
+    need, ulps, max_abs = _scaled_need(yl[(rows_b * sh.data.shape[1] + rows_s).to(dev)].cpu().float(), want.float())
+    val = total_flops / (ms * 1e-3) / 1e12
+    fused = any(k[0] == "ffn" and v is not False for k, v in ljs.nn._fast_layers.items())
+    return {"api": "nn.jit(apply_fn, in_shardings, out_shardings)(params, x) with apply_fn = nn.ffn on NamedSharding operands",
+            "value": val, "unit": UNIT, "ms_per_step": ms, "steps": steps, "ratio_to_layers_value": val / layers_value,
+            "served_by": "layers.FusedTensorParallelFFN (fused reduce-scatter along seq)" if fused else "generic nn.dense plan",
+            "y_shard_shape": list(sh.data.shape),
+            "parity_check": _reduce_check(dist, dev, 8, need, ulps, max_abs, "8 seeded rows of every rank's y shard")}
+
+
 def case1a_leg(ljs, dist, dev, rank, world):
     """BASELINE.json configs[0]: the sharded fp32 matmul of case1a.py on REAL devices.  At every N: the contraction
     dim split over a 1-D mesh of the N GPUs (x P(None,'m'), W P('m',None) -> partial products + all-reduce), literal
@@ -688,6 +742,12 @@ def main():
                                   "the main line's two GEMMs", "value": value, "unit": UNIT, "ms_per_step": ms}
         except Exception as e:   # noqa: BLE001 - never lose the main line over a supplement
             extras["fsdp"] = {"error": repr(e)}
+        # ---- the public, reference-shaped call for the same step ----
+        try:
+            extras["api"] = api_leg(ljs, host_tensors, cfg, args.act, dist, dev, rank, world, total_flops, value)
+        except Exception as e:   # noqa: BLE001
+            extras["api"] = {"error": repr(e)}
+        ljs.nn.invalidate_fast_layers()
         del host_tensors
         torch.cuda.empty_cache()
         # ---- configs[4]: head-sharded causal MHA, B16 S8192 32x128, on the (1,1)/(1,2)/(2,2)/(2,4) mesh ----

@@ -428,7 +428,7 @@ class FlaxAttention:
         w_o, b_o = params["to_out_0"]
         kq, nq = _axes(params["to_q"])
         ko, no = _axes(w_o)
-        if kq or no or len(nq) != 1 or tuple(ko) != tuple(nq) or any(_axes(params[n]) != (kq, nq) for n in ("to_k", "to_v")):
+        if kq or no or len(nq) != 1 or tuple(ko) != tuple(nq) or any(tuple(_axes(params[n])) != (kq, nq) for n in ("to_k", "to_v")):
             return None
         m = nq[0]
         W = mesh.axis_size(m)
