@@ -260,7 +260,10 @@ def invalidate_fast_layers():
 
 def _model_group(rt, mesh, axis):
     """(ranks, process group) of the ranks that differ from this one only along `axis`; collective over the job."""
-    return rt._my_group(mesh.axis_groups((axis,)))
+    ranks, pg = rt._my_group(mesh.axis_groups((axis,)))
+    if pg is None and len(ranks) > 1:      # the axis spans the whole job: the default group, as an explicit handle
+        pg = rt.dist.group.WORLD
+    return ranks, pg
 
 
 def _fast_ffn(x, w1, b1, w2, b2, act, scatter_dim):
