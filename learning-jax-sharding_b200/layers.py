@@ -113,7 +113,9 @@ class PeerReduceScatter:
     W slots of [T/W, N] bf16), a table of every owner's slot pointers for the GEMM epilogue to push into,
     a flag barrier and the local f32 reduction of the W received partials.
 
-    `chunks` = 2 (default when T/W splits into two multiples of 256 rows) pipelines the tail: the product is
+    `chunks` = 2 (opt-in; measured slower than one launch at 2 and at 8 GPUs -- 0.489 vs 0.466 ms per step at 8: the
+    second GEMM at K = d_ff / 8 loses more to two short launches than the hidden half of the tail saves,
+    profiles/r02_bench_n8_chunks*.json) pipelines the tail: the product is
     pushed as two GEMM launches, each covering HALF of every owner's row block, and the barrier + reduction
     of the first half run on a side stream underneath the second GEMM, so only half of the reduction (and one
     barrier) is left after the last GEMM tile.  The side stream is joined before `finish` returns: from outside
@@ -127,7 +129,7 @@ class PeerReduceScatter:
 
     _FLAG_BYTES = 1024
 
-    def __init__(self, T: int, N: int, group, device, chunks: int = 2, batch: int = 1):
+    def __init__(self, T: int, N: int, group, device, chunks: int = 1, batch: int = 1):
         import torch.distributed as dist
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         W = self.world
@@ -244,12 +246,12 @@ class FusedTensorParallelFFN:
     of the partial y is stored from the GEMM epilogue straight into its owner's receive slot over NVLink
     (CUDA-IPC-mapped peer memory), ranks staggered so each destination has one sender at a time; then a
     flag barrier and one local pass summing the W received bf16 partials in f32 (+ b2).  No NCCL on the
-    data path; the first GEMM runs at full size, the second as two launches (half of every owner's block each)
-    so that the barrier + reduction of the first half hide under the second (PeerReduceScatter).  Same result layout as
+    data path; both GEMMs run at full size (`chunks` = 2 splits the second so that the barrier + reduction of the first
+    half hide under the second half: measured slower, PeerReduceScatter).  Same result layout as
     TensorParallelFFN: this rank's sequence block y[rank*T/W : (rank+1)*T/W]; with `batch` > 1 the block of every batch
     item along seq, [batch, seq/W, d_model] (PeerReduceScatter)."""
 
-    def __init__(self, w1, b1, w2, b2, act: str, T: int, group, chunks: int = 2, batch: int = 1):
+    def __init__(self, w1, b1, w2, b2, act: str, T: int, group, chunks: int = 1, batch: int = 1):
         self.w1, self.b1, self.w2, self.b2 = w1, b1, w2, b2
         self.act = _act_code(act, b1 is not None)
         self.d_model, self.F = w1.shape

@@ -44,7 +44,7 @@ def main():
     # fused: GEMM2 epilogue pushes partial tiles into the owners' receive slots over NVLink peer memory
     fused = layers.FusedTensorParallelFFN(bf(w1[:, rank * fl:(rank + 1) * fl].contiguous()), bf(b1[rank * fl:(rank + 1) * fl]),
                                           bf(w2[rank * fl:(rank + 1) * fl].contiguous()), bf(b2), "gelu_tanh", T,
-                                          dist.group.WORLD)
+                                          dist.group.WORLD, chunks=2)
     for it in range(5):     # several steps: both receive buffers and the barrier epochs are exercised
         y = fused.forward(bf(x))
     torch.cuda.synchronize()
@@ -68,7 +68,7 @@ def main():
     # scatter along seq of a [batch, seq] activation (two-level A view): [4, T/4/W, d] per rank, chunks over batch items
     fused_s = layers.FusedTensorParallelFFN(bf(w1[:, rank * fl:(rank + 1) * fl].contiguous()), bf(b1[rank * fl:(rank + 1) * fl]),
                                             bf(w2[rank * fl:(rank + 1) * fl].contiguous()), bf(b2), "gelu_tanh", T,
-                                            dist.group.WORLD, batch=4)
+                                            dist.group.WORLD, batch=4, chunks=2)
     for it in range(3):
         ys = fused_s.forward(bf(x))
     torch.cuda.synchronize()
