@@ -542,6 +542,35 @@ def case1a_leg(ljs, dist, dev, rank, world):
     return out
 
 
+def bind_to_gpu_numa_node(local_rank: int):
+    """Pin this rank's host threads to the CPUs NVML reports as local to its GPU, BEFORE any pinned host buffer is
+    allocated: the staging buffers of the host-buffer step are then first-touched on the GPU's own NUMA node and its
+    DMA does not cross the socket interconnect.  Returns the CPU count bound to, or None."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        idx = local_rank
+        if vis:
+            ids = [v for v in vis.split(",") if v.strip() != ""]
+            try:
+                idx = int(ids[local_rank])
+            except (ValueError, IndexError):
+                idx = local_rank
+        h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+        ncpu = os.cpu_count() or 1
+        words = (ncpu + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = {w * 64 + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return len(cpus)
+    except Exception:   # noqa: BLE001 - no NVML / no permission: run unbound
+        return None
+    return None
+
+
 # ------------------------------------------------------------------------------ GPU legs
 def time_resident(bench, dist, dev, steps, warmup, capi):
     def sync_all():
@@ -599,6 +628,7 @@ def main():
             raise SystemExit("bench.py --gpus N>1 must be launched under torch.distributed.run (one rank per GPU)")
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the sharded layers have no CPU fallback")
+    numa = bind_to_gpu_numa_node(local_rank) if os.environ.get("B200_BENCH_NUMA", "1") != "0" else None
     torch.cuda.set_device(local_rank)
     dist = None
     if world > 1:
@@ -660,6 +690,7 @@ def main():
     # ---------------- parity of what was just timed (every rank, max over ranks) ----------------
     parity = ffn_parity_check(bench, args.act, dist, dev)
     par_name = bench.parallelism_name()
+    bench_depth = bench.e2e_depth
 
     flops_per_launch = total_flops / world / gemm_per_step   # GEMM launches of one step on one GPU share its FLOPs equally
     achieved = flops_per_launch / (kernel_ms * 1e-3) / 1e12
@@ -683,6 +714,7 @@ def main():
                 "host_link_what": "copy-only leg: all ranks upload their x share and download their y share concurrently, "
                                   "no compute; aggregate GB/s over both directions",
                 "achieved_gbs": e2e_bytes_gbs, "frac_of_host_link": e2e_bytes_gbs / link_gbs,
+                "staging_depth": bench_depth, "host_threads_bound_to_gpu_numa_cpus": numa,
                 "compute_ms_per_step": ms},
         "gpu_launches": int(launches),
         "parity_check": parity,

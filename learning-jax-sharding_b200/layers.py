@@ -639,10 +639,13 @@ class FFNBench:
         # waves, on several GPUs a step is one chunk (the layer has its own chunking for the collective)
         self.e2e_chunks = 2 if world == 1 else 1
         self._e2e_step = 0
-        self._x_stages = [self.x_stage, torch.empty_like(self.x)]
-        self._y_devs = [torch.empty((self.T_out, d), dtype=torch.bfloat16, device=dev) for _ in range(2)]
-        self._y_hosts = [self.y_host, torch.empty((self.T_out, d), dtype=torch.bfloat16).pin_memory()]
-        mk = lambda: [[torch.cuda.Event() for _ in range(self.e2e_chunks)] for _ in range(2)]
+        # staging depth: 2 on one GPU; on several GPUs the upload of a step ends with a cross-rank all-gather, so one slow
+        # rank's copy gates everybody -- a third set of buffers absorbs that jitter (B200_E2E_DEPTH to A/B it)
+        self.e2e_depth = D = max(2, int(os.environ.get("B200_E2E_DEPTH", "2" if world == 1 else "3")))
+        self._x_stages = [self.x_stage] + [torch.empty_like(self.x) for _ in range(D - 1)]
+        self._y_devs = [torch.empty((self.T_out, d), dtype=torch.bfloat16, device=dev) for _ in range(D)]
+        self._y_hosts = [self.y_host] + [torch.empty((self.T_out, d), dtype=torch.bfloat16).pin_memory() for _ in range(D - 1)]
+        mk = lambda: [[torch.cuda.Event() for _ in range(self.e2e_chunks)] for _ in range(D)]
         self._in_ev, self._xfree_ev, self._out_ev, self._ycopied_ev = mk(), mk(), mk(), mk()
 
     def host_tensors(self):
@@ -701,7 +704,7 @@ class FFNBench:
             # axis: every rank uploads only ITS 1/W of the rows over PCIe and the ranks all-gather the rest over NVLink
             # (W x 134 MB of host reads would be PCIe-bound).  The layer writes its own output buffer, so the result is
             # moved to this step's staging buffer (a device copy) before the download starts.
-            par = self._e2e_step & 1
+            par = self._e2e_step % self.e2e_depth
             self._e2e_step += 1
             x_stage, y_dev, y_host = self._x_stages[par], self._y_devs[par], self._y_hosts[par]
             if self.mode == "tp":
@@ -732,7 +735,7 @@ class FFNBench:
         # `e2e_drain()` (or a synchronize) has run; it is overwritten two calls later.
         layer, C = self.layer, self.e2e_chunks
         rows = self.T // C
-        par = self._e2e_step & 1
+        par = self._e2e_step % self.e2e_depth
         self._e2e_step += 1
         x_stage, y_dev, y_host = self._x_stages[par], self._y_devs[par], self._y_hosts[par]
         for c in range(C):

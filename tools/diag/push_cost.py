@@ -28,7 +28,7 @@ def timed(fn, iters=30):
     return float(t.item())
 
 
-for (M, N, K) in [(16384, 4096, 2048), (16384, 2048, 4096), (16384, 4096, 8192)]:
+for (M, N, K) in [(16384, 4096, 2048), (16384, 4096, 4096), (16384, 4096, 8192)]:
     a = torch.randn(M, K, device=dev).to(torch.bfloat16)
     w = (torch.randn(K, N, device=dev) / K ** 0.5).to(torch.bfloat16)
     out = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
@@ -44,10 +44,16 @@ for (M, N, K) in [(16384, 4096, 2048), (16384, 2048, 4096), (16384, 4096, 8192)]
     fl = 2.0 * M * N * K
     t_plain = timed(lambda: capi.gemm_bf16(a, w, out=out))
     t_local = timed(lambda: capi.gemm_bf16_scatter(a, w, local_ptrs, R, (rank + 1) % W, N))
+    torch_slots = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+    tptrs = torch.tensor([torch_slots.data_ptr() + j * R * N * 2 for j in range(W)], dtype=torch.int64, device=dev)
+    t_torch = timed(lambda: capi.gemm_bf16_scatter(a, w, tptrs, R, (rank + 1) % W, N))
+    t_rot0 = timed(lambda: capi.gemm_bf16_scatter(a, w, tptrs, R, 0, N))
+    t_plain2 = timed(lambda: capi.gemm_bf16(a, w, out=out))
     t_remote = timed(lambda: capi.gemm_bf16_scatter(a, w, remote_ptrs, R, (rank + 1) % W, N))
     if rank == 0:
         print(f"M={M} N={N} K={K}: plain {t_plain:.4f} ms ({fl / t_plain / 1e9:.0f} TFLOP/s) | scatter local {t_local:.4f} "
               f"({fl / t_local / 1e9:.0f}) | scatter to peers {t_remote:.4f} ({fl / t_remote / 1e9:.0f}); "
-              f"{(world - 1) / world * M * N * 2 / t_remote / 1e6:.0f} GB/s leave each GPU", flush=True)
+              f"{(world - 1) / world * M * N * 2 / t_remote / 1e6:.0f} GB/s leave each GPU | scatter into torch memory {t_torch:.4f}, "
+              f"rot 0 {t_rot0:.4f}, plain again {t_plain2:.4f}", flush=True)
     dist.barrier()
 dist.destroy_process_group()
