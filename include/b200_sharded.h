@@ -147,6 +147,11 @@ typedef struct {
                                            together with the row-block scatter (m_rows_per_block = batch * seq / W) is the
                                            reduce-scatter ALONG SEQ that out_shardings = P('data','model') asks for
                                            (case6_attention.py:161,230), whatever the batch size */
+  int m_block_interleave;               /* row-block scatter only.  0: the kernel finishes one owner's block after the
+                                           other (rank r: r+1, r+2, ..., its own last -- one sender per destination at a
+                                           time).  1: consecutive tiles cycle through the owner blocks, so every wave
+                                           sends to all peers at once and the NVLink traffic is spread evenly over the
+                                           kernel; same result, bit for bit */
 } b200_gemm_args;
 int b200_gemm_bf16_ex(const b200_gemm_args* args, void* stream);
 

@@ -96,7 +96,7 @@ class GemmArgs(ctypes.Structure):
                 ("out_dtype", ctypes.c_int), ("c_block_ptrs", ctypes.c_void_p), ("m_rows_per_block", ctypes.c_int),
                 ("m_block_rot", ctypes.c_int), ("M", ctypes.c_int), ("N", ctypes.c_int), ("K", ctypes.c_int),
                 ("epilogue", ctypes.c_int), ("a_layout", ctypes.c_int), ("tune", GemmTuning),
-                ("a_blocks_inner", ctypes.c_int), ("a_outer_stride", ctypes.c_int)]
+                ("a_blocks_inner", ctypes.c_int), ("a_outer_stride", ctypes.c_int), ("m_block_interleave", ctypes.c_int)]
 
 
 class AttentionBwdArgs(ctypes.Structure):
@@ -480,7 +480,7 @@ def sum_partials_to_bf16(partials, bias=None, out=None):
 
 # ---------------------------------------------------------------- fused GEMM -> reduce-scatter plumbing
 def gemm_bf16_scatter(a, b, block_ptrs, rows_per_block: int, rot: int, ldc: int, *, b_layout=B_KN, a_block_stride: int = 0,
-                      M: int = 0, tune=None, a_view=None):
+                      M: int = 0, tune=None, a_view=None, interleave: bool = False):
     """a[M,K] @ b -> bf16 rows scattered to ``block_ptrs`` (a CUDA int64 tensor of M/rows_per_block base
     pointers, e.g. peer GPUs' receive slots): b200_gemm_bf16_ex with the row-block scatter.  With ``a_block_stride`` > 0
     block j of the product is read from rows [j * a_block_stride, j * a_block_stride + rows_per_block) of ``a`` (``M`` =
@@ -496,6 +496,7 @@ def gemm_bf16_scatter(a, b, block_ptrs, rows_per_block: int, rot: int, ldc: int,
     args.C, args.ldc, args.out_dtype = None, ldc, BF16
     args.c_block_ptrs = block_ptrs.data_ptr()
     args.m_rows_per_block, args.m_block_rot = rows_per_block, rot
+    args.m_block_interleave = int(bool(interleave))
     if a_view is not None:      # two-level view: (rows_per_block, blocks_inner, inner_stride, outer_stride)
         args.a_rows_per_block, args.a_blocks_inner, args.a_block_stride, args.a_outer_stride = (int(v) for v in a_view)
     elif a_block_stride:

@@ -59,6 +59,12 @@ struct GemmParams {
   // to c_block_ptrs[block] (a peer GPU's receive slot, or local memory) at row m % m_rows_per_block.
   void* const* c_block_ptrs;
   int m_rows_per_block, m_block_rot, m_num_blocks;
+  // 1: consecutive tiles cycle through the owner blocks (tile i -> block (i % blocks + rot) % blocks, position i / blocks
+  // inside it) instead of finishing one block after the other: every wave then pushes to ALL peers at once and the NVLink
+  // traffic of a scatter to peer memory is spread over the whole kernel (measured: 677 GB/s per direction is what peer
+  // stores reach here whatever their shape, tools/diag/nvlink_store.cu; block after block, the 7/8 of the tiles that
+  // are remote need more than that while they run and the link idles during the own block)
+  int m_interleave;
   int num_stages;   // smem ring depth actually used (<= Cfg::kStages); tuning experiments only
   int a_mn_major;   // 1: A is stored [K, M] row-major (the transposed operand of a weight-gradient GEMM dW = X^T . dY):
                     // the A tile is loaded as two 64-row-wide MN-major chunks and the MMA reads it with the MN-major flag
@@ -81,6 +87,21 @@ __device__ __forceinline__ float apply_epilogue(float acc, float bias, int epi, 
   if (epi == B200_EPI_BIAS_RELU || epi == B200_EPI_RELU) v = fmaxf(v, 0.0f);
   if (epi == B200_EPI_BIAS_GELU_TANH || epi == B200_EPI_GELU_TANH) v = gelu_tanh_f(v);
   return v;
+}
+
+// first logical row of the 128-row tile (m_blk, cta_rank) after the row-block scatter's permutation
+template <int G>
+__device__ __forceinline__ int scatter_row0(const GemmParams& p, int m_blk, uint32_t cta_rank) {
+  int m0 = (m_blk * G + cta_rank) * kBM;
+  if (p.m_rows_per_block > 0) {
+    if (p.m_interleave) {
+      const int blk = (m_blk % p.m_num_blocks + p.m_block_rot) % p.m_num_blocks;
+      m0 = blk * p.m_rows_per_block + (m_blk / p.m_num_blocks) * (kBM * G) + cta_rank * kBM;
+    } else {
+      m0 = ((m0 / p.m_rows_per_block + p.m_block_rot) % p.m_num_blocks) * p.m_rows_per_block + m0 % p.m_rows_per_block;
+    }
+  }
+  return m0;
 }
 
 __device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, int group_m, int& m_blk,
@@ -158,10 +179,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     for (int tile = worker; tile < num_tiles; tile += num_workers) {
       int m_blk, n_blk;
       tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, m_blk, n_blk);
-      int m0 = (m_blk * G + cta_rank) * kBM;
-      if (p.m_rows_per_block > 0)
-        m0 = ((m0 / p.m_rows_per_block + p.m_block_rot) % p.m_num_blocks) * p.m_rows_per_block +
-             m0 % p.m_rows_per_block;
+      int m0 = scatter_row0<G>(p, m_blk, cta_rank);      // row of the product in "owner block, row inside it" order
       if (p.a_rows_per_block > 0) {
         const int q = m0 / p.a_rows_per_block, r = m0 % p.a_rows_per_block;
         m0 = p.a_blocks_inner > 0
@@ -317,8 +335,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int row_base = (m_blk * G + cta_rank) * kBM + q * 32;       // logical row of lane 0
         __nv_bfloat16* cbase;
         if (p.m_rows_per_block > 0) {
-          const int blk = (row_base / p.m_rows_per_block + p.m_block_rot) % p.m_num_blocks;
-          const int local = row_base % p.m_rows_per_block;
+          const int prow = scatter_row0<G>(p, m_blk, cta_rank) + q * 32;  // (owner block) * rows_per_block + row inside it
+          const int blk = prow / p.m_rows_per_block;
+          const int local = prow % p.m_rows_per_block;
           cbase = p.c_block_ptrs != nullptr
                       ? reinterpret_cast<__nv_bfloat16*>(p.c_block_ptrs[blk]) + static_cast<int64_t>(local) * p.ldc
                       : reinterpret_cast<__nv_bfloat16*>(p.C) +
@@ -599,6 +618,7 @@ extern "C" int b200_gemm_bf16_ex(const b200_gemm_args* args, void* stream) {
   p.m_rows_per_block = args->m_rows_per_block;
   p.m_block_rot = args->m_block_rot;
   p.m_num_blocks = args->m_rows_per_block > 0 ? M / args->m_rows_per_block : 0;
+  p.m_interleave = (args->m_block_interleave && args->m_rows_per_block > 0) ? 1 : 0;
   p.a_mn_major = a_km ? 1 : 0;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const bool kmajor = b_layout == B200_B_NK;

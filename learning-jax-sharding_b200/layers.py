@@ -149,6 +149,9 @@ class PeerReduceScatter:
             while chunks > 1 and (self.R % chunks or (self.R // chunks) % 256):
                 chunks -= 1
         self.chunks = max(chunks, 1)
+        # tile order of the push: cycle through the owners tile by tile (NVLink busy for the whole GEMM) rather than block
+        # after block; B200_TP_INTERLEAVE=0 restores the latter for A/B runs
+        self.interleave = os.environ.get("B200_TP_INTERLEAVE", "1") != "0"
         self.Rc = self.R // self.chunks                         # rows of one chunk inside one owner's block
         self.slot = self.R * N                                  # elements of one receive slot
         total = self._FLAG_BYTES + 2 * W * self.slot * 2        # flags + two receive buffers of W slots
@@ -186,13 +189,14 @@ class PeerReduceScatter:
             inner = self.batch // self.chunks                   # batch items of this launch
             capi.gemm_bf16_scatter(a[c * inner * self.seq:], w, self.c_ptrs[self.buf][c], self.Rc,
                                    (self.rank + 1) % self.world, self.N, M=self.world * self.Rc,
-                                   a_view=(self.rpb, inner, self.seq, self.rpb))
+                                   a_view=(self.rpb, inner, self.seq, self.rpb), interleave=self.interleave)
         elif self.chunks == 1:
-            capi.gemm_bf16_scatter(a, w, self.c_ptrs[self.buf][0], self.R, (self.rank + 1) % self.world, self.N)
+            capi.gemm_bf16_scatter(a, w, self.c_ptrs[self.buf][0], self.R, (self.rank + 1) % self.world, self.N,
+                                   interleave=self.interleave)
         else:
             # logical block j of this launch = rows [c*Rc, (c+1)*Rc) of owner j's row block of `a`
             capi.gemm_bf16_scatter(a[c * self.Rc:], w, self.c_ptrs[self.buf][c], self.Rc, (self.rank + 1) % self.world,
-                                   self.N, a_block_stride=self.R, M=self.world * self.Rc)
+                                   self.N, a_block_stride=self.R, M=self.world * self.Rc, interleave=self.interleave)
 
     def _reduce(self, c: int, bias, out: torch.Tensor):
         """Barrier (every rank's pushes of chunk c have landed), then out rows of chunk c = bf16(sum of the W partials)."""

@@ -375,14 +375,18 @@ def test_gemm_row_block_scatter_and_partial_sum(ljs):
     want = rm.dense_bf16(a, w).float()
     slots = [torch.zeros((R, N), dtype=torch.bfloat16, device="cuda") for _ in range(W)]
     ptrs = torch.tensor([s.data_ptr() for s in slots], dtype=torch.int64, device="cuda")
-    for rot in (0, 1, 3):
+    first = None
+    for rot, interleave in ((0, False), (1, False), (3, False), (0, True), (2, True)):
         for s in slots:
             s.zero_()
-        capi.gemm_bf16_scatter(_dev(a), _dev(w), ptrs, R, rot, N)
+        capi.gemm_bf16_scatter(_dev(a), _dev(w), ptrs, R, rot, N, interleave=interleave)
         torch.cuda.synchronize()
-        # physical block b (rows [bR, (b+1)R) of A) lands in slot b whatever the rotation
+        # physical block b (rows [bR, (b+1)R) of A) lands in slot b whatever the rotation and the tile order
         for b in range(W):
             torch.testing.assert_close(slots[b].cpu().float(), want[b * R:(b + 1) * R], **BF16_TOL)
+        got = torch.cat([s.cpu() for s in slots])
+        first = got if first is None else first
+        assert torch.equal(got, first)                   # the tile order changes no bit
     # local reduction of W bf16 partials (+ bias)
     parts = rm.synthetic((W, R, N), 72).to(torch.bfloat16)
     bias = rm.synthetic((N,), 73, "bias").to(torch.bfloat16)
@@ -391,6 +395,36 @@ def test_gemm_row_block_scatter_and_partial_sum(ljs):
     capi.sum_bf16_partials(pd.data_ptr(), R * N, W, _dev(bias), N, out)
     ref = (parts.float().sum(0).to(torch.bfloat16).float() + bias.float()).to(torch.bfloat16)
     torch.testing.assert_close(out.cpu().float(), ref.float(), rtol=1e-2, atol=1e-2)
+
+
+@pytest.mark.parametrize("causal", [False, True])
+def test_gemm_scatter_two_level_view_and_interleave(ljs):
+    """Reduce-scatter ALONG SEQ of a [batch, seq] activation (b200_gemm_args.a_blocks_inner): owner j's slot receives its
+    seq block of every batch item, [batch, seq / W, N]; with and without the interleaved tile order; in two chunks over the
+    batch items."""
+    capi = ljs.capi
+    Bn, S, N, K, W = 4, 1024, 256, 192, 4
+    rpb = S // W
+    a = rm.synthetic((Bn * S, K), 75).to(torch.bfloat16)
+    w = rm.synthetic((K, N), 76, "weight").to(torch.bfloat16)
+    want = rm.dense_bf16(a, w).float().reshape(Bn, W, rpb, N)
+    ad, wd = _dev(a), _dev(w)
+    for interleave in (False, True):
+        slots = [torch.zeros((Bn * rpb, N), dtype=torch.bfloat16, device="cuda") for _ in range(W)]
+        ptrs = torch.tensor([s.data_ptr() for s in slots], dtype=torch.int64, device="cuda")
+        capi.gemm_bf16_scatter(ad, wd, ptrs, Bn * rpb, 1, N, M=Bn * S, a_view=(rpb, Bn, S, rpb), interleave=interleave)
+        torch.cuda.synchronize()
+        for j in range(W):
+            torch.testing.assert_close(slots[j].cpu().float().reshape(Bn, rpb, N), want[:, j], **BF16_TOL)
+        # two chunks of two batch items each: chunk c writes rows [c * 2 * rpb, (c + 1) * 2 * rpb) of every slot
+        slots2 = [torch.zeros((Bn * rpb, N), dtype=torch.bfloat16, device="cuda") for _ in range(W)]
+        for c in range(2):
+            p2 = torch.tensor([s.data_ptr() + c * 2 * rpb * N * 2 for s in slots2], dtype=torch.int64, device="cuda")
+            capi.gemm_bf16_scatter(ad[c * 2 * S:], wd, p2, 2 * rpb, 3, N, M=W * 2 * rpb, a_view=(rpb, 2, S, rpb),
+                                   interleave=interleave)
+        torch.cuda.synchronize()
+        for j in range(W):
+            assert torch.equal(slots2[j], slots[j])
 
 
 @pytest.mark.parametrize("causal", [False, True])
