@@ -397,7 +397,6 @@ def test_gemm_row_block_scatter_and_partial_sum(ljs):
     torch.testing.assert_close(out.cpu().float(), ref.float(), rtol=1e-2, atol=1e-2)
 
 
-@pytest.mark.parametrize("causal", [False, True])
 def test_gemm_scatter_two_level_view_and_interleave(ljs):
     """Reduce-scatter ALONG SEQ of a [batch, seq] activation (b200_gemm_args.a_blocks_inner): owner j's slot receives its
     seq block of every batch item, [batch, seq / W, N]; with and without the interleaved tile order; in two chunks over the
