@@ -28,7 +28,7 @@ def timed(fn, iters=30):
     return float(t.item())
 
 
-for (M, N, K) in [(16384, 4096, 2048), (16384, 4096, 4096), (16384, 4096, 8192)]:
+for (M, N, K) in [(16384, 4096, 2048), (16384, 4096, 4096), (65536, 4096, 1024)]:
     a = torch.randn(M, K, device=dev).to(torch.bfloat16)
     w = (torch.randn(K, N, device=dev) / K ** 0.5).to(torch.bfloat16)
     out = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
@@ -50,6 +50,7 @@ for (M, N, K) in [(16384, 4096, 2048), (16384, 4096, 4096), (16384, 4096, 8192)]
     t_rot0 = timed(lambda: capi.gemm_bf16_scatter(a, w, tptrs, R, 0, N))
     t_plain2 = timed(lambda: capi.gemm_bf16(a, w, out=out))
     t_remote = timed(lambda: capi.gemm_bf16_scatter(a, w, remote_ptrs, R, (rank + 1) % W, N))
+    t_remote_il = timed(lambda: capi.gemm_bf16_scatter(a, w, remote_ptrs, R, (rank + 1) % W, N, interleave=True))
     if rank == 0:
         print(f"M={M} N={N} K={K}: plain {t_plain:.4f} ms ({fl / t_plain / 1e9:.0f} TFLOP/s) | scatter local {t_local:.4f} "
               f"({fl / t_local / 1e9:.0f}) | scatter to peers {t_remote:.4f} ({fl / t_remote / 1e9:.0f}); "
