@@ -149,9 +149,9 @@ class PeerReduceScatter:
             while chunks > 1 and (self.R % chunks or (self.R // chunks) % 256):
                 chunks -= 1
         self.chunks = max(chunks, 1)
-        # tile order of the push: cycle through the owners tile by tile (NVLink busy for the whole GEMM) rather than block
-        # after block; B200_TP_INTERLEAVE=0 restores the latter for A/B runs
-        self.interleave = os.environ.get("B200_TP_INTERLEAVE", "1") != "0"
+        # tile order of the push: block after block (default), or cycling through the owners tile by tile
+        # (B200_TP_INTERLEAVE=1; measured 1 % slower at 8 GPUs, profiles/r02_nvlink_push.md)
+        self.interleave = os.environ.get("B200_TP_INTERLEAVE", "0") != "0"
         self.Rc = self.R // self.chunks                         # rows of one chunk inside one owner's block
         self.slot = self.R * N                                  # elements of one receive slot
         total = self._FLAG_BYTES + 2 * W * self.slot * 2        # flags + two receive buffers of W slots
@@ -643,9 +643,9 @@ class FFNBench:
         # waves, on several GPUs a step is one chunk (the layer has its own chunking for the collective)
         self.e2e_chunks = 2 if world == 1 else 1
         self._e2e_step = 0
-        # staging depth: 2 on one GPU; on several GPUs the upload of a step ends with a cross-rank all-gather, so one slow
-        # rank's copy gates everybody -- a third set of buffers absorbs that jitter (B200_E2E_DEPTH to A/B it)
-        self.e2e_depth = D = max(2, int(os.environ.get("B200_E2E_DEPTH", "2" if world == 1 else "3")))
+        # staging depth 2 (B200_E2E_DEPTH to A/B it: 3 and 4 measured no faster at 8 GPUs, where the step is bound by
+        # the host link -- profiles/r02_nvlink_push.md)
+        self.e2e_depth = D = max(2, int(os.environ.get("B200_E2E_DEPTH", "2")))
         self._x_stages = [self.x_stage] + [torch.empty_like(self.x) for _ in range(D - 1)]
         self._y_devs = [torch.empty((self.T_out, d), dtype=torch.bfloat16, device=dev) for _ in range(D)]
         self._y_hosts = [self.y_host] + [torch.empty((self.T_out, d), dtype=torch.bfloat16).pin_memory() for _ in range(D - 1)]
