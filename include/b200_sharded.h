@@ -214,6 +214,19 @@ int b200_attention_fwd_lse(const void* Q, const void* K, const void* V, void* O,
                            int causal, void* stream);
 
 /*
+ * Blockwise ("ring") attention over a sequence-sharded K / V -- the literal layout of the reference, where the activations
+ * stay split along S over 'model' (case6_attention.py:105-107,114-116) and XLA would all-gather K and V for the score
+ * einsum (:125,133).  Instead every device runs b200_attention_fwd_lse on its query block against ONE key/value block at a
+ * time (its own, then the blocks passed round the ring) and folds each result into a running pair with this call:
+ *   lse' = log2(2^lse_acc + 2^lse_blk),  acc' = acc 2^(lse_acc - lse') + o_blk 2^(lse_blk - lse')
+ * acc [B, S, H, D] f32 and lse_acc [B, H, S] f32 are the running pair (first != 0 initialises them from the block),
+ * o_blk [B, S, H, D] bf16 / lse_blk [B, H, S] f32 one block's result; all contiguous.  After the last block
+ * b200_cast_f32_to_bf16(acc) is the attention output.  D in {64, 128}.
+ */
+int b200_attention_combine(float* acc, float* lse_acc, const void* o_blk, const float* lse_blk, int B, int S, int H, int D,
+                           int first, void* stream);
+
+/*
  * Attention backward: dQ, dK, dV of O = softmax(scale Q K^T [+ causal mask]) V given dO, O and the forward's lse2 --
  * the part of jax.grad through FlaxAttention.__call__ (case6_attention.py:121-135) that the reference's train_step runs
  * (case6_attention.py:206-220).  Layouts as in b200_attention_fwd; strides (elements) for

@@ -43,6 +43,7 @@ EXPORTED_SYMBOLS = (
     "b200_adam_step",
     "b200_attention_fwd_lse",
     "b200_attention_bwd",
+    "b200_attention_combine",
     "b200_comm_unique_id",
     "b200_mesh_create",
     "b200_mesh_axis_comm",
@@ -147,6 +148,7 @@ def load():
     lib.b200_attention_fwd_ex.argtypes = [ctypes.POINTER(AttentionArgs), vp]
     lib.b200_ffn_fwd_static_scratch.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp]
     lib.b200_attention_fwd_lse.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32] + [i64] * 12 + [f32, i32, vp]
+    lib.b200_attention_combine.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp]
     lib.b200_attention_bwd.argtypes = [ctypes.POINTER(AttentionBwdArgs), vp]
     lib.b200_ffn_fwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp]
     lib.b200_cast_f32_to_bf16.argtypes = [vp, vp, i64, vp]
@@ -390,6 +392,24 @@ def attention_fwd_lse(q, k, v, *, scale=None, causal=False, variant=0):
     lse = torch.empty((B, H, Sq), dtype=torch.float32, device=q.device)
     out = attention_fwd(q, k, v, scale=scale, causal=causal, lse=lse, variant=variant)
     return out, lse
+
+
+def attention_combine(acc, lse_acc, o_blk, lse_blk, *, first: bool):
+    """Fold one key/value block's attention result (o_blk bf16 [B,S,H,D], lse_blk f32 [B,H,S]) into the running pair
+    (acc f32 [B,S,H,D], lse_acc f32 [B,H,S]) in place -- b200_attention_combine, the merge step of ring attention."""
+    _require_cuda(acc, lse_acc, o_blk, lse_blk)
+    B, S, H, D = o_blk.shape
+    if acc.shape != o_blk.shape or acc.dtype != torch.float32 or o_blk.dtype != torch.bfloat16 or \
+            lse_acc.shape != (B, H, S) or lse_blk.shape != (B, H, S) or lse_acc.dtype != torch.float32 or \
+            lse_blk.dtype != torch.float32:
+        raise B200Error("attention_combine: acc f32 / o_blk bf16 [B,S,H,D], lse_acc / lse_blk f32 [B,H,S]")
+    if not (acc.is_contiguous() and o_blk.is_contiguous() and lse_acc.is_contiguous() and lse_blk.is_contiguous()):
+        raise B200Error("attention_combine takes contiguous tensors")
+    with torch.cuda.device(acc.device):
+        rc = load().b200_attention_combine(_ptr(acc), _ptr(lse_acc), _ptr(o_blk), _ptr(lse_blk), B, S, H, D, int(bool(first)),
+                                           _stream(acc))
+    _check(rc, "b200_attention_combine")
+    return acc
 
 
 def attention_bwd(q, k, v, o, do, lse2, *, scale=None, causal=False):

@@ -81,6 +81,60 @@ static int grid_for(int64_t work_items) {
   return static_cast<int>(blocks);
 }
 
+
+// Blockwise ("ring") attention, merge step: fold the result of one more key/value block into the running result of a
+// query block.  o_blk [rows, D] bf16 is that block's softmax-normalised output, lse_blk [rows] its log2-sum-exp
+// (b200_attention_fwd_lse); acc [rows, D] f32 / lse_acc [rows] are the running pair:
+//   lse' = log2(2^lse_acc + 2^lse_blk),  acc' = acc * 2^(lse_acc - lse') + o_blk * 2^(lse_blk - lse').
+// first != 0 starts the running pair from the block.  Row r of acc is (b, s, h) of the [B, S, H, D] tensor; the lse
+// arrays are [B, H, S] as the attention kernels write them.  One warp per row, 16-byte accesses.
+template <int D>
+__global__ void __launch_bounds__(256) attention_combine_kernel(float* __restrict__ acc, float* __restrict__ lse_acc,
+                                                               const __nv_bfloat16* __restrict__ o_blk,
+                                                               const float* __restrict__ lse_blk, int64_t rows, int S,
+                                                               int H, int first) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+  for (int64_t r = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; r < rows; r += warps) {
+    const int h = static_cast<int>(r % H);
+    const int64_t bs = r / H;
+    const int s = static_cast<int>(bs % S);
+    const int64_t b = bs / S;
+    const int64_t li = (b * H + h) * S + s;
+    const float lb = lse_blk[li];
+    float w_old = 0.f, w_new = 1.f, l_new = lb;
+    if (!first) {
+      const float la = lse_acc[li];
+      const float m = fmaxf(la, lb);
+      l_new = m + log2f(exp2f(la - m) + exp2f(lb - m));
+      w_old = exp2f(la - l_new);
+      w_new = exp2f(lb - l_new);
+    }
+    __syncwarp();
+    if (lane == 0) lse_acc[li] = l_new;
+    constexpr int kPer = D / 32;                       // 2 or 4 elements per lane
+    float* a = acc + r * D + lane * kPer;
+    const __nv_bfloat16* o = o_blk + r * D + lane * kPer;
+    if (kPer == 4) {
+      const uint2 raw = *reinterpret_cast<const uint2*>(o);
+      const float2 o01 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.x));
+      const float2 o23 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.y));
+      float4 v = first ? make_float4(0.f, 0.f, 0.f, 0.f) : *reinterpret_cast<const float4*>(a);
+      v.x = v.x * w_old + o01.x * w_new;
+      v.y = v.y * w_old + o01.y * w_new;
+      v.z = v.z * w_old + o23.x * w_new;
+      v.w = v.w * w_old + o23.y * w_new;
+      *reinterpret_cast<float4*>(a) = v;
+    } else {
+      const float2 o01 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(o));
+      float2 v = first ? make_float2(0.f, 0.f) : *reinterpret_cast<const float2*>(a);
+      v.x = v.x * w_old + o01.x * w_new;
+      v.y = v.y * w_old + o01.y * w_new;
+      *reinterpret_cast<float2*>(a) = v;
+    }
+  }
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -121,6 +175,28 @@ extern "C" int b200_sum_partials_to_bf16(const float* src, int64_t src_stride, i
   sum_partials_kernel<<<grid_for(n / 4), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       src, src_stride, nsrc, reinterpret_cast<const __nv_bfloat16*>(bias), cols > 0 ? cols : 4,
       reinterpret_cast<__nv_bfloat16*>(dst), n);
+  B200_CUDA_CHECK(cudaGetLastError());
+  launch_counter().fetch_add(1);
+  return B200_OK;
+}
+
+extern "C" int b200_attention_combine(float* acc, float* lse_acc, const void* o_blk, const float* lse_blk, int B, int S, int H,
+                                      int D, int first, void* stream) {
+  B200_REQUIRE(acc && lse_acc && o_blk && lse_blk, "b200_attention_combine: null pointer");
+  B200_REQUIRE(B > 0 && S > 0 && H > 0 && (D == 64 || D == 128), "b200_attention_combine: bad sizes (head dim 64 or 128)");
+  B200_REQUIRE((reinterpret_cast<uintptr_t>(acc) | reinterpret_cast<uintptr_t>(o_blk)) % 16 == 0,
+               "b200_attention_combine: acc and o_blk must be 16-byte aligned");
+  const int64_t rows = static_cast<int64_t>(B) * S * H;
+  int64_t blocks = (rows + 7) / 8;
+  const int64_t cap = static_cast<int64_t>(num_sms()) * 8;
+  if (blocks > cap) blocks = cap;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (D == 128)
+    attention_combine_kernel<128><<<static_cast<int>(blocks), 256, 0, st>>>(acc, lse_acc, reinterpret_cast<const __nv_bfloat16*>(o_blk),
+                                                                         lse_blk, rows, S, H, first);
+  else
+    attention_combine_kernel<64><<<static_cast<int>(blocks), 256, 0, st>>>(acc, lse_acc, reinterpret_cast<const __nv_bfloat16*>(o_blk),
+                                                                        lse_blk, rows, S, H, first);
   B200_CUDA_CHECK(cudaGetLastError());
   launch_counter().fetch_add(1);
   return B200_OK;

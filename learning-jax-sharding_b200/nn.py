@@ -219,15 +219,59 @@ def merge_heads(x: ShardedArray) -> ShardedArray:
                         shards)
 
 
+def _ring_attention(q: ShardedArray, k: ShardedArray, v: ShardedArray, scale, causal: bool) -> ShardedArray:
+    """Blockwise attention for q, k, v all split along S over the same mesh axes (the literal case6 layout,
+    case6_attention.py:105-107,114-116): K / V are never gathered.  Every device attends its query block to one key/value
+    block at a time -- its own first, then the blocks that travel round the ring of the S-sharding group, the transfer of
+    the next block running under the attention of the current one -- and merges the per-block results through their
+    log-sum-exp (b200_attention_fwd_lse + b200_attention_combine).  With `causal`, blocks that lie entirely in the future
+    of the query block are skipped and only the diagonal block is masked."""
+    rt = _rt.get_runtime()
+    comp = _rt.local_compute()
+    mesh = q.sharding.mesh
+    groups = mesh.axis_groups(_axes(k)[1])
+    pos = {d: i for g in groups for i, d in enumerate(g)}
+    W = len(groups[0])
+    cur = {d: torch.stack([k.shard(d), v.shard(d)]) for d in rt.local_device_ids}
+    acc, lse, started = {}, {}, {}
+    for t in range(W):
+        nxt, pending = rt.ring_shift_start(cur, groups) if t + 1 < W else (None, [])
+        for d in rt.local_device_ids:
+            src = (pos[d] - t) % W                      # whose block this device holds at step t
+            if causal and src > pos[d]:
+                continue                                # every key of that block is later than every query here
+            ql = q.shard(d)
+            o_b, lse_b = comp.attention_fwd_lse(ql, cur[d][0], cur[d][1], scale=scale, causal=causal and src == pos[d])
+            if d not in acc:
+                acc[d] = torch.empty(ql.shape, dtype=torch.float32, device=ql.device)
+                lse[d] = torch.empty_like(lse_b)
+            comp.attention_combine(acc[d], lse[d], o_b.contiguous(), lse_b, first=d not in started)
+            started[d] = True
+        if nxt is not None:
+            rt.ring_shift_finish(pending)
+            cur = nxt
+    out = {d: comp.cast_f32_to_bf16(acc[d]) for d in rt.local_device_ids}
+    return ShardedArray(q.shape, torch.bfloat16, q.sharding, out)
+
+
 def dot_product_attention(q: ShardedArray, k: ShardedArray, v: ShardedArray, *, scale: Optional[float] = None,
-                          causal: bool = False) -> ShardedArray:
+                          causal: bool = False, ring: Optional[bool] = None) -> ShardedArray:
     """softmax(scale q k^T) v on (b, S, N, D) arrays (case6_attention.py:121-135).  Batch and head
-    dims may be sharded (no communication: head-sharded attention); a sequence-sharded q keeps its
-    query block while k and v are all-gathered along S (the literal case6 layout)."""
+    dims may be sharded (no communication: head-sharded attention).  A sequence-sharded q keeps its query block; when k
+    and v are split along S the same way (the literal case6 layout) the key/value blocks go round a ring and are never
+    gathered (``ring``: None = that choice, False = all-gather k and v along S instead, what XLA would do)."""
     rt = _rt.get_runtime()
     comp = _rt.local_compute()
     mesh = q.sharding.mesh
     qa, ka = _axes(q), _axes(k)
+    same_blocks = bool(ka[1]) and tuple(qa[1]) == tuple(ka[1]) and tuple(_axes(v)[1]) == tuple(ka[1]) and \
+        q.shape[1] == k.shape[1] and tuple(qa[0]) == tuple(ka[0]) and tuple(qa[2]) == tuple(ka[2])
+    if ring is None:
+        ring = same_blocks
+    if ring:
+        if not same_blocks:
+            raise ValueError("ring attention needs q, k and v split along S over the same mesh axes, with Sq == Sk")
+        return _ring_attention(q, k, v, scale, causal)
     if ka[1]:
         full_kv = NamedSharding(mesh, _spec([ka[0], (), ka[2], ka[3]]))
         k = reshard(k, full_kv)
@@ -359,7 +403,8 @@ class FlaxAttention:
     out-projection row-parallel with a reduce-scatter back to the sequence-sharded output."""
 
     def __init__(self, query_dim: int, heads: int = 8, dim_head: int = 64, causal: bool = False,
-                 layout: str = "literal"):
+                 layout: str = "literal", ring: Optional[bool] = None):
+        self.ring = ring                                   # literal layout: None / True = ring attention, False = all-gather K, V
         self.query_dim, self.heads, self.dim_head = query_dim, heads, dim_head
         self.scale = dim_head ** -0.5                      # case6_attention.py:51
         self.causal = causal
@@ -479,7 +524,7 @@ class FlaxAttention:
         q, k, v = (split_heads(t, self.heads) for t in (q, k, v))               # :109-112
         names4 = ("batch", "embed", None, None) if self.layout == "literal" else ("batch", None, "heads", None)
         q, k, v = (with_logical_constraint(t, names4) for t in (q, k, v))       # :114-116
-        o = dot_product_attention(q, k, v, scale=self.scale, causal=self.causal)   # :121-133
+        o = dot_product_attention(q, k, v, scale=self.scale, causal=self.causal, ring=self.ring)   # :121-133
         o = merge_heads(o)                                                  # :135
         o = with_logical_constraint(o, ("batch", "kv", "heads"))            # :137
         w_o, b_o = params["to_out_0"]

@@ -139,6 +139,19 @@ class VirtualRuntime:
         self._log("all_to_all", groups, bufs)
         return out
 
+    def ring_shift_start(self, bufs, groups):
+        """Every device's buffer moves to the NEXT member of its group (the last one's to the first): returns
+        ({device: buffer received from the previous member}, pending).  In-process: nothing is pending."""
+        out = {}
+        for g in groups:
+            for i, d in enumerate(g):
+                out[d] = bufs[g[i - 1]]
+        self._log("ring_shift", groups, bufs)
+        return out, []
+
+    def ring_shift_finish(self, pending):
+        return None
+
     def exchange(self, bufs, src_index, wanted, global_shape, dtype):
         """Generic resharding: ``src_index[d]`` is the global slice device d holds (for all devices),
         ``wanted[d]`` the slice it must end up with.  In-process copy between virtual devices."""
@@ -282,6 +295,32 @@ class DistributedRuntime:
                     recv = gathered
         self.collective_log.append(("all_to_all", len(g), t.numel() * t.element_size()))
         return {self.rank: torch.cat(recv, dim=concat_dim).contiguous()}
+
+    def ring_shift_start(self, bufs, groups):
+        """This rank's buffer goes to the next member of its group, the previous member's arrives: point-to-point
+        send / receive, asynchronous -- the caller computes on what it holds and calls ring_shift_finish(pending) before
+        touching the received buffer (ring attention: the transfer of block t+1 runs under the attention of block t)."""
+        g = None
+        for grp in groups:
+            if self.rank in grp:
+                g = list(grp)
+        if g is None:
+            raise RuntimeError(f"rank {self.rank} is in none of the groups {groups}")
+        send = bufs[self.rank].contiguous()
+        if len(g) == 1:
+            return {self.rank: send}, []
+        i = g.index(self.rank)
+        recv = torch.empty_like(send)
+        ops = [self.dist.P2POp(self.dist.isend, send, g[(i + 1) % len(g)]),
+               self.dist.P2POp(self.dist.irecv, recv, g[(i - 1) % len(g)])]
+        pending = self.dist.batch_isend_irecv(ops)
+        self.collective_log.append(("ring_shift", len(g), send.numel() * send.element_size()))
+        return {self.rank: recv}, (pending, send)          # `send` is kept alive until the transfer has completed
+
+    def ring_shift_finish(self, pending):
+        if pending:
+            for req in pending[0]:
+                req.wait()
 
     def exchange(self, bufs, src_index, wanted, global_shape, dtype):
         """Generic resharding over the whole job: all-gather every rank's shard (padded to a common

@@ -87,3 +87,19 @@ def attention_fwd_lse(q, k, v, *, scale=None, causal=False):
 def attention_bwd(q, k, v, o, do, lse2, *, scale=None, causal=False):
     dq, dk, dv, _ = rm.attention_core_grads(q, k, v, do, scale, causal)
     return dq, dk, dv
+
+
+def attention_combine(acc, lse_acc, o_blk, lse_blk, *, first):
+    """b200_attention_combine on the host (f64 inside)."""
+    lb = lse_blk.double()
+    if first:
+        acc.copy_(o_blk.to(F32))
+        lse_acc.copy_(lse_blk)
+        return acc
+    la = lse_acc.double()
+    ln = torch.log2(torch.exp2(la) + torch.exp2(lb))
+    w_old = torch.exp2(la - ln).permute(0, 2, 1).unsqueeze(-1)
+    w_new = torch.exp2(lb - ln).permute(0, 2, 1).unsqueeze(-1)
+    acc.copy_((acc.double() * w_old + o_blk.double() * w_new).to(F32))
+    lse_acc.copy_(ln.to(F32))
+    return acc

@@ -57,6 +57,18 @@ def _worker(rank, world, port, results):
         yy = model(model.shard_params(host, tp, rules), ljs.device_put(xh, xs))
     want_a = rm.mha_forward(xh, host, 4, 8).float()
     ok["attn_heads"] = torch.allclose(yy.device_buffers[0].float(), want_a[:, 4 * rank:4 * rank + 4], rtol=2e-2, atol=2e-2)
+    # (3b) the LITERAL annotation set (activations split along S over 'model'): ring attention over two processes --
+    # point-to-point send / receive of the K, V blocks -- causal and not
+    rules_l = (("batch", "data"), ("embed", "model"), ("hidden", "model"))
+    for causal in (False, True):
+        model_l = ljs.nn.FlaxAttention(32, heads=4, dim_head=8, causal=causal)
+        rt.collective_log.clear()
+        with tp, ljs.nn.axis_rules(rules_l):
+            yl = model_l(model_l.shard_params(host, tp, rules_l), ljs.device_put(xh, xs))
+        want_l = rm.mha_forward(xh, host, 4, 8, causal).float()
+        ok[f"attn_literal_ring_causal{int(causal)}"] = (
+            torch.allclose(yl.device_buffers[0].float(), want_l[:, 4 * rank:4 * rank + 4], rtol=2e-2, atol=2e-2)
+            and "ring_shift" in [n for n, _, _ in rt.collective_log])
     t = torch.arange(4 * 8 * 6, dtype=torch.float32).reshape(4, 8, 6)
     z = ljs.reshard(ljs.device_put(t, ns(P(None, "model"))), ns(P(None, None, "model")))
     ok["all_to_all"] = torch.equal(z.device_buffers[0], t[:, :, 3 * rank:3 * rank + 3])

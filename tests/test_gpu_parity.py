@@ -340,6 +340,42 @@ def test_case6_literal_module_against_golden(ljs):
     torch.testing.assert_close(yh.global_array()[::2, ::4].float(), GOLD["case6_literal_y"].float(), **BF16_TOL)
 
 
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("d", [64, 128])
+def test_ring_attention_virtual_mesh(ljs, causal, d):
+    """Ring attention on 4 virtual devices of one GPU (S split 4-way over 'model'): b200_attention_fwd_lse per key/value
+    block + b200_attention_combine, against the oracle's unsharded attention, both tolerance tiers; and the merge kernel
+    alone against its formula."""
+    ljs.init_virtual(4, "cuda:0")
+    mesh = ljs.Mesh(ljs.create_device_mesh((1, 4)), ("data", "model"))
+    sh = ljs.NamedSharding(mesh, ljs.PartitionSpec("data", "model", None, None))
+    B, S, H = 2, 1024, 2
+    q, k, v = (rm.synthetic((B, S, H, d), 110 + i).to(torch.bfloat16) for i in range(3))
+    n0 = ljs.capi.launch_count()
+    o = ljs.nn.dot_product_attention(ljs.device_put(q, sh), ljs.device_put(k, sh), ljs.device_put(v, sh), causal=causal)
+    blocks = 10 if causal else 16                      # (query block, key block) pairs that are not fully masked
+    assert ljs.capi.launch_count() - n0 == 2 * blocks + 4            # attention + merge per pair, one cast per device
+    assert tuple(o.device_buffers[0].shape) == (B, S // 4, H, d)
+    _check_attention(o.global_array(), q, k, v, causal, f"ring attention d{d} causal={causal}")
+
+
+def test_attention_combine_formula(ljs):
+    capi = ljs.capi
+    B, S, H, D = 2, 300, 3, 128
+    o1, o2 = (rm.synthetic((B, S, H, D), 120 + i).to(torch.bfloat16).cuda() for i in range(2))
+    l1, l2 = (rm.synthetic((B, H, S), 122 + i).cuda() * 3 for i in range(2))
+    acc = torch.full((B, S, H, D), float("nan"), device="cuda")
+    lse = torch.full((B, H, S), float("nan"), device="cuda")
+    capi.attention_combine(acc, lse, o1, l1, first=True)
+    assert torch.equal(acc, o1.float()) and torch.equal(lse, l1)
+    capi.attention_combine(acc, lse, o2, l2, first=False)
+    ln = torch.log2(torch.exp2(l1.double()) + torch.exp2(l2.double()))
+    w1 = torch.exp2(l1.double() - ln).permute(0, 2, 1).unsqueeze(-1)
+    w2 = torch.exp2(l2.double() - ln).permute(0, 2, 1).unsqueeze(-1)
+    torch.testing.assert_close(lse.double(), ln, rtol=0, atol=1e-5)
+    torch.testing.assert_close(acc.double(), o1.double() * w1 + o2.double() * w2, rtol=1e-5, atol=1e-5)
+
+
 def test_case5_literal_dense_against_golden(ljs):
     ljs.init_virtual(4, "cuda:0")
     mesh = ljs.Mesh(ljs.create_device_mesh((2, 2)), ("data", "model"))

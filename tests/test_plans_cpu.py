@@ -98,7 +98,8 @@ def test_attention_module_matches_oracle(ljs, cpu_checker, layout, causal):
     got = y.global_array().float()
     torch.testing.assert_close(got, want.float(), rtol=2e-2, atol=2e-2)
     if layout == "literal":
-        assert "all_gather" in names and "all_to_all" in names              # K/V gather along S, M->S re-split
+        # weights gathered, K / V blocks passed round the ring of the S-sharding group (never gathered), M->S re-split
+        assert "all_gather" in names and "all_to_all" in names and "ring_shift" in names
     else:
         assert "reduce_scatter" in names                                     # row-parallel out-projection
 
@@ -181,3 +182,31 @@ def test_product_path_refuses_cpu_tensors(ljs):
     b = ljs.device_put(B, s.replicate(axis=0, keepdims=True))
     with pytest.raises(ljs.capi.B200Error):
         ljs.lax.dot(a, b)
+
+
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("mesh_shape", [(1, 4), (2, 2), (2, 4)])
+def test_ring_attention_equals_gathered_attention(ljs, cpu_checker, causal, mesh_shape):
+    """q, k, v split along S over 'model' (case6_attention.py:114-116): the ring plan (blocks travel, per-block results
+    merged through their log-sum-exp) gives what gathering K and V along S gives, moves W - 1 blocks per device instead of
+    gathering, and skips the blocks a causal mask hides completely."""
+    n = mesh_shape[0] * mesh_shape[1]
+    ljs.init_virtual(n, "cpu")
+    rt = ljs.get_runtime()
+    mesh = ljs.Mesh(ljs.create_device_mesh(mesh_shape), ("data", "model"))
+    sh = ljs.NamedSharding(mesh, ljs.PartitionSpec("data", "model", None, None))
+    q, k, v = (rm.synthetic((4, 64, 2, 16), 70 + i).to(torch.bfloat16) for i in range(3))
+    qs, ks, vs = (ljs.device_put(t, sh) for t in (q, k, v))
+    rt.collective_log.clear()
+    ring = ljs.nn.dot_product_attention(qs, ks, vs, causal=causal)                     # default for this layout
+    names = [nm for nm, _, _ in rt.collective_log]
+    assert names.count("ring_shift") == mesh_shape[1] - 1 and "all_gather" not in names
+    rt.collective_log.clear()
+    gathered = ljs.nn.dot_product_attention(qs, ks, vs, causal=causal, ring=False)
+    assert "all_gather" in [nm for nm, _, _ in rt.collective_log]
+    want = rm.attention_core(q, k, v, causal=causal).float()
+    torch.testing.assert_close(gathered.global_array().float(), want, rtol=2e-2, atol=2e-2)
+    torch.testing.assert_close(ring.global_array().float(), want, rtol=2e-2, atol=2e-2)
+    assert ring.sharding.spec == qs.sharding.spec
+    with pytest.raises(ValueError, match="ring attention needs"):
+        ljs.nn.dot_product_attention(ljs.device_put(q, ljs.NamedSharding(mesh, ljs.PartitionSpec("data"))), ks, vs, ring=True)
