@@ -127,8 +127,10 @@ def attention_sum_loss_grads(module, params, x: ShardedArray) -> Dict[str, Shard
     axis in the backward (x and dy are replicated over it, every head's chain is local).  Keys of the result: "to_q", "to_k",
     "to_v", "to_out_0.kernel", "to_out_0.bias"."""
     from . import nn as _nn
+    if module.layout == "literal":
+        return _attention_sum_loss_grads_literal(module, params, x)
     if module.layout != "heads":
-        raise NotImplementedError("attention_sum_loss_grads covers layout='heads' (the BASELINE.json case6 annotation set)")
+        raise NotImplementedError(f"attention_sum_loss_grads: unknown layout {module.layout!r}")
     rt = _rt.get_runtime()
     comp = _rt.local_compute()
     mesh = x.sharding.mesh
@@ -167,6 +169,99 @@ def attention_sum_loss_grads(module, params, x: ShardedArray) -> Dict[str, Shard
         target = w_o if n == "to_out_0.kernel" else params[n]
         grads[n] = ShardedArray(target.shape, torch.float32, target.sharding, part)
     # d sum(y) / d bias = number of (batch, position) rows, in the bias's dtype chain (bf16) like the oracle
+    nrows = float(torch.tensor(float(B * S)).to(torch.bfloat16))
+    grads["to_out_0.bias"] = ShardedArray(b_o.shape, torch.float32, b_o.sharding,
+                                          {d: torch.full_like(t, nrows, dtype=torch.float32) for d, t in b_o.local_shards.items()})
+    return grads
+
+
+def _attention_sum_loss_grads_literal(module, params, x: ShardedArray) -> Dict[str, ShardedArray]:
+    """The same gradients under the reference's LITERAL annotation set (case6_attention.py:56-59,85-88,105-116,137,141 with
+    the rules of :183-187): activations split along S over 'model', to_q / to_k / to_v split on their rows (embed), to_out_0
+    on its columns.  The backward is the transpose of the forward's resharding points, one by one:
+        :141  all-to-all M -> S            | dy = ones arrives S-sharded; its M-sharded form is ones again
+        :139  column-parallel to_out_0     | dWo = o^T . dy (all-reduce over 'data'); dO = dy . Wo^T is a PARTIAL sum over the
+                                           | kernel's column shards
+        :137  all-gather of o along S      | ... which a reduce-scatter along S over 'model' both completes and re-splits
+        :121-135 attention, K / V whole    | b200_attention_bwd on the local query block against the gathered K, V (for a
+                                           | causal mask: the keys up to the block's last query); dK, dV partials cover every
+                                           | key -> reduce-scatter along S; dQ is local
+        :96-99 Dense on gathered kernels   | dW = x^T . dq|dk|dv summed over every token shard (all-reduce over 'data' and
+                                           | 'model'), then cut to the kernel's row shard
+    Every weight gradient is rounded to bf16 once, after its full sum, like the cotangent of an unsharded bf16 dot."""
+    from . import nn as _nn
+    rt = _rt.get_runtime()
+    comp = _rt.local_compute()
+    mesh = x.sharding.mesh
+    H, D = module.heads, module.dim_head
+    B, S, M = x.shape
+    w_o, b_o = params["to_out_0"]
+    q, k, v = (_nn.dense(x, params[n]) for n in ("to_q", "to_k", "to_v"))                     # :96-99, S-sharded like x
+    q, k, v = (_nn.with_logical_constraint(t, ("batch", "embed", None)) for t in (q, k, v))   # :105-107
+    q4, k4, v4 = (_nn.split_heads(t, H) for t in (q, k, v))                                    # :109-112
+    qa = _axes(q4)
+    data_axes, seq_axes = tuple(qa[0]), tuple(qa[1])
+    if qa[2] or qa[3]:
+        raise NotImplementedError("the literal layout keeps heads and head dim unsharded")
+    ko, no = _axes(w_o)
+    if ko or (seq_axes and tuple(no) != seq_axes):
+        raise NotImplementedError("to_out_0 must be column-parallel over the axis that splits S (the literal rules)")
+    kv_spec = NamedSharding(mesh, _spec([data_axes, (), (), ()]))
+    kf, vf = reshard(k4, kv_spec), reshard(v4, kv_spec)                                        # K, V whole along S
+    seq_groups = mesh.axis_groups(seq_axes) if seq_axes else None
+    o_sh, res = {}, {}
+    for d in rt.local_device_ids:
+        ql = q4.shard(d)
+        f1 = q4.index_of(d)[1].stop
+        kl, vl = kf.shard(d), vf.shard(d)
+        if module.causal:
+            kl, vl = kl[:, :f1].contiguous(), vl[:, :f1].contiguous()                          # keys up to the block's last query
+        o_l, lse_l = comp.attention_fwd_lse(ql, kl, vl, scale=module.scale, causal=module.causal)
+        o_sh[d], res[d] = o_l, (ql, kl, vl, lse_l)
+    o4 = ShardedArray(q4.shape, torch.bfloat16, q4.sharding, o_sh)
+    o_g = _nn.with_logical_constraint(_nn.merge_heads(o4), ("batch", "kv", "heads"))          # :135-137: gathered along S
+    parts = {n: {} for n in ("to_q", "to_k", "to_v", "to_out_0.kernel")}
+    do_part = {}
+    for d in rt.local_device_ids:
+        og = o_g.shard(d)
+        rows = og.shape[0] * og.shape[1]
+        wo_l = _to_bf16(w_o.shard(d))                                                          # [inner, M / m]
+        dy = torch.ones((rows, wo_l.shape[1]), dtype=torch.bfloat16, device=og.device)
+        parts["to_out_0.kernel"][d] = comp.gemm_bf16_tn(og.reshape(rows, -1), dy, out_dtype=torch.float32)
+        do_part[d] = comp.gemm_bf16(dy, wo_l, b_layout=1, out_dtype=torch.float32).reshape(og.shape)   # partial over columns
+    if seq_axes:
+        do_part = rt.reduce_scatter(do_part, seq_groups, dim=1)                                # sum over 'model', split S again
+    dk_part, dv_part = {}, {}
+    for d in rt.local_device_ids:
+        ql, kl, vl, lse_l = res[d]
+        do_l = comp.cast_f32_to_bf16(do_part[d].contiguous()).reshape(ql.shape)
+        dq, dk, dv = comp.attention_bwd(ql, kl, vl, o_sh[d], do_l, lse_l, scale=module.scale, causal=module.causal)
+        xs = x.shard(d)
+        x2 = _to_bf16(xs.reshape(-1, M))
+        parts["to_q"][d] = comp.gemm_bf16_tn(x2, dq.reshape(x2.shape[0], -1), out_dtype=torch.float32)
+        full = (ql.shape[0], S) + tuple(ql.shape[2:])
+        for dst, g in ((dk_part, dk), (dv_part, dv)):
+            buf = torch.zeros(full, dtype=torch.float32, device=g.device)                      # keys this block never sees: zero
+            buf[:, :g.shape[1]] = comp.cast_bf16_to_f32(g)
+            dst[d] = buf
+    if seq_axes:
+        dk_part, dv_part = rt.reduce_scatter(dk_part, seq_groups, dim=1), rt.reduce_scatter(dv_part, seq_groups, dim=1)
+    for d in rt.local_device_ids:
+        x2 = _to_bf16(x.shard(d).reshape(-1, M))
+        for n, g in (("to_k", dk_part[d]), ("to_v", dv_part[d])):
+            gb = comp.cast_f32_to_bf16(g.contiguous()).reshape(x2.shape[0], -1)
+            parts[n][d] = comp.gemm_bf16_tn(x2, gb, out_dtype=torch.float32)
+    grads = {}
+    for n, part in parts.items():
+        axes = data_axes if n == "to_out_0.kernel" else data_axes + seq_axes                   # the token shards summed over
+        if axes:
+            part = rt.all_reduce(part, mesh.axis_groups(axes))
+        part = {d: comp.cast_bf16_to_f32(comp.cast_f32_to_bf16(t.contiguous())) for d, t in part.items()}
+        if n == "to_out_0.kernel":
+            grads[n] = ShardedArray(w_o.shape, torch.float32, w_o.sharding, part)
+        else:
+            full = ShardedArray(params[n].shape, torch.float32, NamedSharding(mesh, _spec([(), ()])), part)
+            grads[n] = reshard(full, params[n].sharding)                                       # local cut to the row shard
     nrows = float(torch.tensor(float(B * S)).to(torch.bfloat16))
     grads["to_out_0.bias"] = ShardedArray(b_o.shape, torch.float32, b_o.sharding,
                                           {d: torch.full_like(t, nrows, dtype=torch.float32) for d, t in b_o.local_shards.items()})

@@ -88,6 +88,14 @@ def _worker(rank, world, port, results):
     ok["attn_grads"] = all(
         torch.allclose(grads[n].device_buffers[0], want_g[n], rtol=3e-2, atol=3e-2 * want_g[n].abs().max().item())
         for n in ("to_q", "to_k", "to_v", "to_out_0.kernel", "to_out_0.bias"))
+    # (5) the same train_step gradients under the LITERAL annotation set on a (1,2) mesh: S split over two processes
+    model_l = ljs.nn.FlaxAttention(32, heads=4, dim_head=8)
+    with tp, ljs.nn.axis_rules(rules_l):
+        params_l = model_l.shard_params(host, tp, rules_l)
+        grads_l = ljs.train.attention_sum_loss_grads(model_l, params_l, ljs.device_put(xh, xs))
+    ok["attn_grads_literal"] = all(
+        torch.allclose(grads_l[n].global_array(), want_g[n], rtol=3e-2, atol=3e-2 * want_g[n].abs().max().item())
+        for n in ("to_q", "to_k", "to_v", "to_out_0.kernel", "to_out_0.bias"))
     results[rank] = ok
     rt.barrier()
     torch.distributed.destroy_process_group()

@@ -638,16 +638,18 @@ def test_attention_backward_config_size_sample(ljs, causal):
 
 
 @pytest.mark.parametrize("causal", [False, True])
-def test_attention_module_train_step_literal_size(ljs, causal):
+@pytest.mark.parametrize("layout", ["heads", "literal"])
+def test_attention_module_train_step_literal_size(ljs, causal, layout):
     """train_step of the attention module (case6_attention.py:206-220) at the script's literal size (x (8,256,640), 8 heads x
-    64) in the head-sharded layout on four virtual devices of one GPU: gradients in the parameters' shardings against autodiff
-    of the unsharded f64 formula, then one Adam step through b200_adam_step."""
+    64) on four virtual devices of one GPU, in the head-sharded layout and under the script's LITERAL annotation set (S split
+    over 'model', kernels split on embed): gradients in the parameters' shardings against autodiff of the unsharded f64
+    formula, then one Adam step through b200_adam_step."""
     ljs.init_virtual(4, "cuda:0")
     mesh = ljs.Mesh(ljs.create_device_mesh((2, 2)), ("data", "model"))
-    model = ljs.nn.FlaxAttention(640, heads=8, dim_head=64, causal=causal, layout="heads")
+    model = ljs.nn.FlaxAttention(640, heads=8, dim_head=64, causal=causal, layout=layout)
     host = model.init_host(seed=1)
     host["to_out_0"] = (host["to_out_0"][0], rm.synthetic((640,), 9, "bias"))
-    rules = (("batch", "data"), ("heads", "model"), ("hidden", "model"))
+    rules = (("batch", "data"), ("heads" if layout == "heads" else "embed", "model"), ("hidden", "model"))
     x_host = rm.synthetic((8, 256, 640), 5)
     x = ljs.device_put(x_host, ljs.NamedSharding(mesh, ljs.PartitionSpec("data", "model")))
     params = model.shard_params(host, mesh, rules)

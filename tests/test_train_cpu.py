@@ -97,3 +97,35 @@ def test_attention_module_train_step_matches_oracle(ljs, cpu_checker, causal):
         # the first Adam step is -lr * sign(g): compare where the gradient is well away from zero (its sign is then settled)
         mask = want[name].abs() > 0.1 * want[name].abs().max()
         torch.testing.assert_close(state.params[name].global_array()[mask], k2[mask], rtol=0, atol=2e-5)
+
+
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("mesh_shape", [(2, 2), (1, 4)])
+def test_attention_module_train_step_literal_annotations(ljs, cpu_checker, causal, mesh_shape):
+    """The same train_step under the reference's LITERAL annotation set (activations split along S over 'model', q/k/v
+    kernels split on their rows, to_out_0 on its columns -- case6_attention.py:56-59,85-88,105-116,183-187): gradients in the
+    parameters' shardings against autodiff of the unsharded formula; the backward's collectives are the transposes of the
+    forward's resharding points (reduce-scatter along S for dO, dK, dV; all-reduce of the weight gradients)."""
+    from tests.test_plans_cpu import _attention_setup
+    mesh, model, host, rules, x_host, x_sharding = _attention_setup(ljs, "literal", mesh_shape=mesh_shape, causal=causal)
+    rt = ljs.get_runtime()
+    params = model.shard_params(host, mesh, rules)
+    assert tuple(params["to_q"].device_buffers[0].shape) == (64 // mesh_shape[1], 64)
+    x = ljs.device_put(x_host, x_sharding)
+    want = rm.mha_sum_loss_grads(x_host, host, model.heads, model.dim_head, causal)
+    with mesh, ljs.nn.axis_rules(rules):
+        rt.collective_log.clear()
+        grads = ljs.train.attention_sum_loss_grads(model, params, x)
+        names = [n for n, _, _ in rt.collective_log]
+        assert names.count("reduce_scatter") == 3                              # dO, dK, dV along S over 'model'
+        for name, g in grads.items():
+            target = params["to_out_0"][0 if name.endswith("kernel") else 1] if name.startswith("to_out_0") else params[name]
+            assert g.sharding.same_layout(target.sharding, target.shape), name
+            scale = want[name].abs().max().item()
+            torch.testing.assert_close(g.global_array(), want[name], rtol=3e-2, atol=3e-2 * scale, msg=lambda m, n=name: n + ": " + m)
+        state = ljs.train.attention_train_state(model, params, ljs.train.adam(learning_rate=0.001))
+        state = ljs.train.attention_train_step(model, state, x)
+        y = model(ljs.train.attention_params_of(state), x)                     # the updated parameters run forward
+    assert state.step == 1 and y.shape == x.shape
+    moved = (state.params["to_q"].global_array() - host["to_q"]).abs()
+    assert 0.5e-3 < moved.mean().item() <= 1.01e-3                             # first Adam step: |update| = lr almost everywhere
