@@ -177,6 +177,18 @@ def main():
         print(f"[rank {rank}] FlaxAttention layout={layout} on mesh {d_ax}x{world // d_ax} via nn.jit (fused layer: {fast}): "
               f"max_abs={(got6 - ref6).abs().max().item():.3e} {'OK' if good else 'FAIL'}", flush=True)
         ok &= good and (fast or layout == "literal")
+        if layout == "literal":
+            # K / V blocks went round the ring of the S-sharding group (NCCL send / receive), never gathered
+            ringed = "ring_shift" in [n for n, _, _ in rt.collective_log] or world // d_ax == 1
+            # ... and the train_step gradients under the same annotations (reduce-scatter along S, all-reduce of dW)
+            with mesh6, ljs.nn.axis_rules(rules):
+                g6 = ljs.train.attention_sum_loss_grads(model, prm, x6)
+            w6 = rm.mha_sum_loss_grads(x6_host, p6, 8, 64)
+            gg = all(bool(torch.allclose(g6[n].global_array().cpu(), w6[n], rtol=3e-2, atol=3e-2 * w6[n].abs().max().item()))
+                     for n in ("to_q", "to_k", "to_v", "to_out_0.kernel", "to_out_0.bias"))
+            print(f"[rank {rank}] literal layout: ring attention used: {ringed}; train_step gradients "
+                  f"{'OK' if gg else 'FAIL'}", flush=True)
+            ok &= ringed and gg
     # the sharded fp32 lax.dot of case1a/1b/2/3/4 on real devices: the literal 2x4 PositionalSharding layouts need 8 GPUs;
     # at any size the 1-D mesh form of BASELINE.json configs[0]
     gA = torch.Generator().manual_seed(0)
