@@ -363,6 +363,12 @@ int b200_peer_copy2d(void* dst, int64_t dst_pitch_bytes, const void* src, int64_
  * the persistent GEMM.  Reaches NVLink bandwidth where strided copy-engine copies do not. */
 int b200_peer_gather(void* const* src_bases_dev, int world, int rank, int64_t src_off_bytes, int64_t src_pitch_bytes,
                      void* dst, int64_t dst_pitch_bytes, int rows, int64_t width_bytes, int ctas, void* stream);
+/* The PUSH form of the same all-gather: this rank's contiguous shard (`bytes` at `src`) is stored at dst_off_bytes of EVERY
+ * rank's gathered buffer (dst_bases_dev: DEVICE array of `world` base pointers, own buffer included).  Peer stores are posted,
+ * so a few CTAs reach NVLink's write bandwidth where pulls are bound by load latency.  The caller synchronises the ranks
+ * around it (b200_peer_barrier: the destination buffers are free before, every push has landed after). */
+int b200_peer_push(void* const* dst_bases_dev, int world, int rank, int64_t dst_off_bytes, const void* src, int64_t bytes,
+                   int ctas, void* stream);
 int b200_peer_barrier(void* const* flag_ptrs_dev, int rank, int world, uint32_t epoch, void* stream);
 int b200_sum_bf16_partials(const void* src, int64_t src_stride, int nsrc, const void* bias, int64_t cols, void* dst,
                            int64_t n, void* stream);

@@ -62,6 +62,7 @@ EXPORTED_SYMBOLS = (
     "b200_peer_free",
     "b200_peer_copy2d",
     "b200_peer_gather",
+    "b200_peer_push",
     "b200_peer_barrier",
     "b200_sum_bf16_partials",
     "b200_random_fill",
@@ -140,6 +141,7 @@ def load():
     lib.b200_peer_free.argtypes = [vp]
     lib.b200_peer_copy2d.argtypes = [vp, i64, vp, i64, i64, i64, vp]
     lib.b200_peer_gather.argtypes = [vp, i32, i32, i64, i64, vp, i64, i32, i64, i32, vp]
+    lib.b200_peer_push.argtypes = [vp, i32, i32, i64, vp, i64, i32, vp]
     lib.b200_peer_barrier.argtypes = [vp, i32, i32, ctypes.c_uint32, vp]
     lib.b200_sum_bf16_partials.argtypes = [vp, i64, i32, vp, i64, vp, i64, vp]
     lib.b200_gemm_f32.argtypes = [vp, i64, i64, vp, i64, i64, vp, i64, i64, i32, i32, i32, i32, i32, vp]
@@ -641,10 +643,23 @@ def peer_open(handle: bytes) -> int:
     return int(ptr.value)
 
 
-def peer_barrier(flag_ptrs, rank: int, world: int, epoch: int):
+def peer_barrier(flag_ptrs, rank: int, world: int, epoch: int, stream=None):
+    st = _stream(flag_ptrs) if stream is None else ctypes.c_void_p(stream.cuda_stream)
     with torch.cuda.device(flag_ptrs.device):
-        rc = load().b200_peer_barrier(_ptr(flag_ptrs), rank, world, epoch & 0xFFFFFFFF, _stream(flag_ptrs))
+        rc = load().b200_peer_barrier(_ptr(flag_ptrs), rank, world, epoch & 0xFFFFFFFF, st)
     _check(rc, "b200_peer_barrier")
+
+
+def peer_push(dst_bases, world: int, rank: int, dst_off: int, src: torch.Tensor, ctas: int, stream):
+    """This rank's contiguous shard ``src`` into offset ``dst_off`` (bytes) of every rank's gathered buffer (dst_bases: CUDA
+    int64 tensor of base pointers), enqueued on ``stream`` -- b200_peer_push."""
+    _require_cuda(dst_bases, src)
+    if not src.is_contiguous():
+        raise B200Error("peer_push takes a contiguous source")
+    with torch.cuda.device(src.device):
+        rc = load().b200_peer_push(_ptr(dst_bases), world, rank, dst_off, _ptr(src), src.numel() * src.element_size(), ctas,
+                                   ctypes.c_void_p(stream.cuda_stream))
+    _check(rc, "b200_peer_push")
 
 
 def sum_bf16_partials(src_ptr: int, src_stride: int, nsrc: int, bias, cols: int, out):

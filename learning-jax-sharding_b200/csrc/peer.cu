@@ -113,9 +113,50 @@ __global__ void __launch_bounds__(256) peer_gather_kernel(const uint8_t* const* 
   }
 }
 
+// The PUSH form of the weight all-gather: this rank's contiguous shard goes to the same offset of every rank's gathered
+// buffer (its own included) with plain 16-byte stores.  Stores to peer memory are posted -- they reach the ~677 GB/s per
+// direction that NVLink gives peer writes here with a few CTAs (tools/diag/nvlink_store.cu) -- whereas the pull form above
+// is bound by the round-trip latency of its loads.  Each CTA starts at a different peer so that all links carry traffic
+// from the first instruction on.
+__global__ void __launch_bounds__(256) peer_push_kernel(uint8_t* const* __restrict__ dst_bases, int world, int rank,
+                                                       int64_t dst_off_bytes, const uint8_t* __restrict__ src,
+                                                       int64_t units) {
+  const int64_t per_cta = (units + gridDim.x - 1) / gridDim.x;
+  const int64_t u_begin = per_cta * blockIdx.x;
+  const int64_t u_end = u_begin + per_cta < units ? u_begin + per_cta : units;
+  const uint4* s4 = reinterpret_cast<const uint4*>(src);
+  for (int64_t u0 = u_begin + threadIdx.x; u0 < u_end; u0 += 4 * 256) {
+    uint4 v[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      if (u0 + k * 256 < u_end) v[k] = s4[u0 + k * 256];
+    for (int pp = 0; pp < world; ++pp) {
+      const int p = (rank + 1 + pp + blockIdx.x) % world;
+      uint4* d4 = reinterpret_cast<uint4*>(dst_bases[p] + dst_off_bytes);
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (u0 + k * 256 < u_end) d4[u0 + k * 256] = v[k];
+    }
+  }
+}
+
 }  // namespace b200
 
 using namespace b200;
+
+extern "C" int b200_peer_push(void* const* dst_bases_dev, int world, int rank, int64_t dst_off_bytes, const void* src,
+                              int64_t bytes, int ctas, void* stream) {
+  B200_REQUIRE(dst_bases_dev && src && world >= 1 && rank >= 0 && rank < world && bytes > 0, "b200_peer_push: bad arguments");
+  B200_REQUIRE(bytes % 16 == 0 && dst_off_bytes % 16 == 0 && reinterpret_cast<uintptr_t>(src) % 16 == 0,
+               "b200_peer_push: offset, size and source must be multiples of 16 bytes");
+  B200_REQUIRE(ctas >= 1 && ctas <= 1024, "b200_peer_push: ctas must be in [1, 1024]");
+  peer_push_kernel<<<ctas, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<uint8_t* const*>(dst_bases_dev), world, rank, dst_off_bytes, reinterpret_cast<const uint8_t*>(src),
+      bytes / 16);
+  B200_CUDA_CHECK(cudaGetLastError());
+  launch_counter().fetch_add(1);
+  return B200_OK;
+}
 
 extern "C" int b200_peer_gather(void* const* src_bases_dev, int world, int rank, int64_t src_off_bytes,
                                 int64_t src_pitch_bytes, void* dst, int64_t dst_pitch_bytes, int rows,

@@ -542,6 +542,107 @@ class PeerGatherFFN:
         return self.y
 
 
+class _RawCudaBuffer:
+    """A device allocation made outside torch (b200_peer_alloc: CUDA-IPC-exported), exposed through
+    __cuda_array_interface__ so that torch can view it without copying."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes // 2,), "typestr": "<u2", "data": (ptr, False), "version": 2}
+
+
+def _bf16_view(ptr: int, rows: int, cols: int, device) -> torch.Tensor:
+    return torch.as_tensor(_RawCudaBuffer(ptr, rows * cols * 2), device=device).view(torch.bfloat16).view(rows, cols)
+
+
+class PushGatherFFN:
+    """FSDP layout with the weight all-gather done by PUSHING: every rank stores its dim0-shard of W1 and W2 straight into
+    every rank's gathered matrices (CUDA-IPC-shared, double-buffered by call parity) with one small kernel per weight
+    (`b200_peer_push`: posted 16-byte stores over NVLink, a few CTAs that co-reside with the persistent GEMM), framed by two
+    flag barriers on a side stream -- "the destination buffer is free on every rank" before, "every shard has landed" after.
+    A dim0-shard is a contiguous row block of the gathered matrix, so the push is one contiguous copy per peer and the GEMMs
+    read plain row-major weights.  As in the other FSDP layers the gather of W1 for the NEXT call runs under this call's
+    second GEMM, and nothing gathered outlives the call that uses it."""
+
+    _FLAG_BYTES = 1024
+
+    def __init__(self, w1_shard, b1, w2_shard, b2, act: str, T_local: int, group, ctas: int = 0, prefetch: bool = True):
+        import torch.distributed as dist
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        W = self.world
+        self.b1, self.b2 = b1, b2
+        self.act = _act_code(act, b1 is not None)
+        self.k1, self.F = w1_shard.shape
+        self.k2, self.d_model = w2_shard.shape
+        self.T = T_local
+        self.prefetch = prefetch
+        self.ctas = ctas or int(os.environ.get("B200_FSDP_PUSH_CTAS", "32"))
+        dev = w1_shard.device
+        self.w1s, self.w2s = w1_shard.contiguous(), w2_shard.contiguous()
+        self.n1, self.n2 = W * self.k1 * self.F * 2, W * self.k2 * self.d_model * 2       # bytes of the gathered matrices
+        total = self._FLAG_BYTES + 2 * (self.n1 + self.n2)
+        self.base, handle = capi.peer_alloc(total)
+        mine = torch.tensor(list(handle), dtype=torch.uint8, device=dev)
+        handles = [torch.empty_like(mine) for _ in range(W)]
+        dist.all_gather(handles, mine, group=group)
+        self.peer_base = [self.base if p == self.rank else capi.peer_open(bytes(handles[p].cpu().tolist()))
+                          for p in range(W)]
+        self.bases = torch.tensor(self.peer_base, dtype=torch.int64, device=dev)          # flags sit at offset 0 of each
+        off = lambda buf, which: self._FLAG_BYTES + buf * (self.n1 + self.n2) + (0 if which == 0 else self.n1)
+        self._off = off
+        self.w1g = [_bf16_view(self.base + off(b, 0), W * self.k1, self.F, dev) for b in range(2)]
+        self.w2g = [_bf16_view(self.base + off(b, 1), W * self.k2, self.d_model, dev) for b in range(2)]
+        self.h = torch.empty((T_local, self.F), dtype=torch.bfloat16, device=dev)
+        self.y = torch.empty((T_local, self.d_model), dtype=torch.bfloat16, device=dev)
+        self.cs = torch.cuda.Stream(device=dev)
+        self.ready = [[torch.cuda.Event() for _ in range(2)] for _ in range(2)]      # [buf][which]: gathered and visible
+        self.read = [[torch.cuda.Event() for _ in range(2)] for _ in range(2)]       # [buf][which]: my GEMMs have read it
+        self.epoch = 0
+        self._call = 0
+        self._w1_inflight = -1
+        dist.barrier(group=group)
+
+    def _gather(self, which: int, buf: int):
+        """Queue the all-gather of weight `which` (0 = W1, 1 = W2) into buffer `buf` on the side stream."""
+        cs = self.cs
+        cs.wait_event(self.read[buf][which])                  # this rank's GEMMs that read the buffer last are done ...
+        self.epoch += 1
+        capi.peer_barrier(self.bases, self.rank, self.world, self.epoch, stream=cs)     # ... and so are everybody's
+        shard = self.w1s if which == 0 else self.w2s
+        nbytes = shard.numel() * 2
+        capi.peer_push(self.bases, self.world, self.rank, self._off(buf, which) + self.rank * nbytes, shard, self.ctas, cs)
+        self.epoch += 1
+        capi.peer_barrier(self.bases, self.rank, self.world, self.epoch, stream=cs)     # every rank's shard has landed here
+        self.ready[buf][which].record(cs)
+
+    def forward(self, x: torch.Tensor, record=None) -> torch.Tensor:
+        main = torch.cuda.current_stream(x.device)
+        call = self._call
+        self._call += 1
+        buf = call & 1 if self.prefetch else 0
+        if self._w1_inflight != call:
+            self._gather(0, buf)
+        self._gather(1, buf)
+        if self.prefetch:
+            self._gather(0, buf ^ 1)                          # for the next call: runs under this call's second GEMM
+            self._w1_inflight = call + 1
+        main.wait_event(self.ready[buf][0])
+        if record is not None:
+            record("start")
+        capi.gemm_bf16(x, self.w1g[buf], bias=self.b1, epilogue=self.act, out=self.h)
+        if record is not None:
+            record("gemm1")
+        self.read[buf][0].record(main)
+        main.wait_event(self.ready[buf][1])
+        if record is not None:
+            record("start")
+        capi.gemm_bf16(self.h, self.w2g[buf], bias=self.b2, epilogue=capi.EPI_BIAS if self.b2 is not None else capi.EPI_NONE,
+                       out=self.y)
+        if record is not None:
+            record("gemm2")
+        self.read[buf][1].record(main)
+        return self.y
+
+
 # ------------------------------------------------------------------------ bench harness glue
 def _synthetic(shape, seed, kind, fan_in=None, device="cuda"):
     """Seeded synthetic tensors of SURVEY.md §8d, generated on the host like the oracle's."""
@@ -594,6 +695,15 @@ class FFNBench:
             # with the next call's W1 prefetched, each weight has a whole GEMM to arrive under: one chunk keeps the GEMMs at
             # full waves (a d_model/4-column chunk of GEMM2 is 1.7 waves of tiles)
             chunks = int(os.environ.get("B200_FSDP_CHUNKS", "1" if prefetch else str(chunks)))
+            if fsdp_mode == "push":
+                try:
+                    self.layer = PushGatherFFN(*shard, act, tl, group, prefetch=prefetch)
+                    self.collective = (f"weight shards PUSHED into every rank's gathered matrices over NVLink peer memory "
+                                       f"({self.layer.ctas} CTAs beside the GEMM, flag barriers on a side stream)" +
+                                       (", W1 of the next call prefetched under GEMM2" if prefetch else ""))
+                except Exception as e:   # noqa: BLE001
+                    if rank == 0:
+                        print(f"[bench] push gather unavailable ({e!r}); using NCCL", file=sys.stderr, flush=True)
             if fsdp_mode in ("peer", "peer_kernel"):
                 try:
                     self.layer = PeerGatherFFN(*shard, act, tl, group, chunks=chunks, prefetch=prefetch,

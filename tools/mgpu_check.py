@@ -120,6 +120,16 @@ def main():
     good = bool((err <= 2e-2 * want[rank * tl:(rank + 1) * tl].abs() + 2e-2).all())
     print(f"[rank {rank}] FSDP peer-pull gather: max_abs={err.max().item():.3e} {'OK' if good else 'FAIL'}", flush=True)
     ok &= good
+    ph = layers.PushGatherFFN(bf(w1[rank * k1:(rank + 1) * k1].contiguous()), bf(b1), bf(w2[rank * k2:(rank + 1) * k2].contiguous()),
+                              bf(b2), "gelu_tanh", tl, dist.group.WORLD)
+    for it in range(4):                           # both buffer parities, barrier epochs, the prefetch of the next call's W1
+        y = ph.forward(bf(x[rank * tl:(rank + 1) * tl].contiguous()))
+    torch.cuda.synchronize()
+    err = (y.cpu().float() - want[rank * tl:(rank + 1) * tl]).abs()
+    good = bool((err <= 2e-2 * want[rank * tl:(rank + 1) * tl].abs() + 2e-2).all())
+    good &= bool(torch.equal(ph.w1g[0].cpu(), w1.to(torch.bfloat16))) and bool(torch.equal(ph.w2g[1].cpu(), w2.to(torch.bfloat16)))
+    print(f"[rank {rank}] FSDP push gather: max_abs={err.max().item():.3e} {'OK' if good else 'FAIL'}", flush=True)
+    ok &= good
     # the generic host layer on a real 1 x world mesh: nn.ffn with NCCL collectives
     P = ljs.PartitionSpec
     mesh = ljs.Mesh(ljs.create_device_mesh((1, world)), ("data", "model"))
