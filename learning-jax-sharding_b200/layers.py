@@ -575,7 +575,7 @@ class PushGatherFFN:
         self.k2, self.d_model = w2_shard.shape
         self.T = T_local
         self.prefetch = prefetch
-        self.ctas = ctas or int(os.environ.get("B200_FSDP_PUSH_CTAS", "32"))
+        self.ctas = ctas or int(os.environ.get("B200_FSDP_PUSH_CTAS", "16"))
         dev = w1_shard.device
         self.w1s, self.w2s = w1_shard.contiguous(), w2_shard.contiguous()
         self.n1, self.n2 = W * self.k1 * self.F * 2, W * self.k2 * self.d_model * 2       # bytes of the gathered matrices
