@@ -29,6 +29,12 @@
 #include "host_common.h"
 #include "sm100_ptx.cuh"
 
+#ifndef B200_ATTN_LATE_PWAIT
+#define B200_ATTN_LATE_PWAIT 0   // 1: wait for "P[b] read by P.V of tile T-2" right before the P store instead of before the exp
+                                 // pass.  Measured 8-12 % SLOWER (interleaved A/B, tools/diag/attn_ab.py: 974 vs 1097 TFLOP/s at
+                                 // B8 S4096 32x128, 572 vs 636 at head dim 64): the early wait paces the two softmax groups
+#endif
+
 namespace b200 {
 
 constexpr int kA8BM = 128;      // query rows per item
@@ -367,7 +373,8 @@ attention_fwd8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
           l_part *= exp2_approx(m_local - m_used);
           m_local = m_used;
         }
-        if (__any_sync(0xffffffffu, rescale)) {
+        const bool any_rescale = __any_sync(0xffffffffu, rescale);
+        if (any_rescale) {
           // O may only be touched once every P.V issued so far (tile T-1 is the last) has completed; P.V(T) cannot
           // start before this warp has delivered P(T) below, and a rescale by tile T+1 waits for P.V(T) in turn.
           mbar_wait(&pv_done[(T - 1) & 1], ((T - 1) >> 1) & 1);
@@ -382,9 +389,11 @@ attention_fwd8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
             tmem_st_32x32(o_all + c * 32, r);
           }
           tmem_wait_st();
-        } else if (T >= 2) {
-          mbar_wait(&pv_done[b], ((T - 2) >> 1) & 1);   // P[b] has been read by P.V of tile T-2
         }
+#if !B200_ATTN_LATE_PWAIT
+        else if (T >= 2) mbar_wait(&pv_done[b], ((T - 2) >> 1) & 1);   // P[b] has been read by P.V of tile T-2
+#endif
+        // (P[b] is written only after the exp pass: its "read by P.V of tile T-2" wait sits there, under the MUFU work)
         // p = exp2(s * scale_log2 - m_used) -> bf16 pairs in place -> TMEM P[b]
         const uint64_t negm2 = pack_f32x2(-m_used, -m_used);
         uint64_t sum2[2] = {0ull, 0ull};
@@ -402,6 +411,10 @@ attention_fwd8_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
           unpack_f32x2(sum2[0], a0, a1);
           unpack_f32x2(sum2[1], b0, b1);
           l_part += (a0 + a1) + (b0 + b1);
+        }
+        if (B200_ATTN_LATE_PWAIT && !any_rescale && T >= 2) {   // (the rescale path has already waited for P.V of tile T-1)
+          mbar_wait(&pv_done[b], ((T - 2) >> 1) & 1);   // P[b] has been read by P.V of tile T-2
+          tc_fence_after();
         }
         {
           const uint32_t(&pp0)[32] = *reinterpret_cast<const uint32_t(*)[32]>(&s[0]);

@@ -29,6 +29,12 @@
 #include "host_common.h"
 #include "sm100_ptx.cuh"
 
+#ifndef B200_ATTN_LATE_PWAIT
+#define B200_ATTN_LATE_PWAIT 0   // 1: wait for "P[b] read by P.V of tile T-2" right before the P store instead of before the exp
+                                 // pass.  Measured 8-12 % SLOWER (interleaved A/B, tools/diag/attn_ab.py: 974 vs 1097 TFLOP/s at
+                                 // B8 S4096 32x128, 572 vs 636 at head dim 64): the early wait paces the two softmax groups
+#endif
+
 namespace b200 {
 
 #ifndef B200_ATTN_PROFILE
@@ -40,8 +46,13 @@ namespace b200 {
 #endif
 
 #ifndef B200_ATTN9_OVERLAP
-#define B200_ATTN9_OVERLAP 0    // 1: second half of the S load under the max of the first, first half of the P store under
-#endif                          //    the exp of the second (A/B: profiles/r01_attention_v9_ab.log)
+#define B200_ATTN9_OVERLAP 0    // (not compatible with the late P-buffer wait: an r01 experiment, kept for the record)
+#endif
+#if B200_ATTN9_OVERLAP
+#error "B200_ATTN9_OVERLAP stores half of P before the P-buffer wait: rebuild r01's attention9.cu to repeat that A/B"
+#endif
+// (1 = second half of the S load under the max of the first, first half of the P store under the exp of the second; A/B in
+//  profiles/r01_attention_v9_ab.log: no gain)
 #ifndef B200_ATTN9_POLY
 #define B200_ATTN9_POLY 0       // n > 0: every (1 << n)-th pair of exp2 goes to a degree-3 polynomial on the FMA pipe
 #endif
@@ -522,7 +533,8 @@ attention_fwd9_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
           l_part *= exp2_approx(m_local - m_used);
           m_local = m_used;
         }
-        if (__any_sync(0xffffffffu, rescale)) {
+        const bool any_rescale = __any_sync(0xffffffffu, rescale);
+        if (any_rescale) {
           // O may only be touched once every P.V issued so far (tile T-1 is the last) has completed; P.V(T) cannot
           // start before this warp has delivered P(T) below, and a rescale by tile T+1 waits for P.V(T) in turn.
           mbar_wait(&pv_done[(T - 1) & 1], ((T - 1) >> 1) & 1);
@@ -537,9 +549,11 @@ attention_fwd9_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
             tmem_st_32x32(o_all + c * 32, r);
           }
           tmem_wait_st();
-        } else if (T >= 2) {
-          mbar_wait(&pv_done[b], ((T - 2) >> 1) & 1);   // P[b] has been read by P.V of tile T-2
         }
+#if !B200_ATTN_LATE_PWAIT
+        else if (T >= 2) mbar_wait(&pv_done[b], ((T - 2) >> 1) & 1);   // P[b] has been read by P.V of tile T-2
+#endif
+        // (P[b] is written only after the exp pass: its "read by P.V of tile T-2" wait sits there, under the MUFU work)
         PROF_MARK9(4);
         // p = exp2(s * scale_log2 - m_used) -> bf16 pairs in place -> TMEM P[b]
         const uint64_t negm2 = pack_f32x2(-m_used, -m_used);
@@ -594,6 +608,10 @@ attention_fwd9_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
           l_part += (a0 + a1) + (b0 + b1);
         }
         PROF_MARK9(5);
+        if (B200_ATTN_LATE_PWAIT && !any_rescale && T >= 2) {   // (the rescale path has already waited for P.V of tile T-1)
+          mbar_wait(&pv_done[b], ((T - 2) >> 1) & 1);   // P[b] has been read by P.V of tile T-2
+          tc_fence_after();
+        }
         {
           const uint32_t(&pp0)[32] = *reinterpret_cast<const uint32_t(*)[32]>(&s[0]);
           const uint32_t(&pp1)[32] = *reinterpret_cast<const uint32_t(*)[32]>(&s[32]);
