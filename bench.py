@@ -157,6 +157,17 @@ def train_kernel_sample(dev, peaks):
             "adam_frac_of_hbm_peak": 28.0 * n / (ms_adam * 1e-3) / 1e9 / peaks.get("hbm_gbs", 6551.4)}
 
 
+def workload_config(workload, cfg, act, world):
+    """The `config` object of the JSON line: what is computed, identical in the product arm and in `--impl reference` (how each
+    arm computes it is described elsewhere in its line: `implementation`, `cpu_baseline.sample`)."""
+    mode = cfg.get("parallelism", "tp")
+    return {"workload": workload, "batch": cfg["batch"], "seq_len": cfg["seq"], "d_model": cfg["d_model"], "d_ff": cfg["d_ff"],
+            "activation": act, "bias": True, "flops_per_step": ffn_flops(cfg),
+            "parallelism": "1 GPU" if world == 1 else (f"{mode}{world}" + (" (W1 columns / W2 rows over 'model')" if mode == "tp"
+                                                                       else " (tokens and weight rows over 'data')")),
+            "l2": "inputs larger than L2 (x 134 MB, W1 134 MB, W2 134 MB, h 537 MB per step vs 126 MB L2)"}
+
+
 def ffn_flops(cfg):
     return 4.0 * cfg["batch"] * cfg["seq"] * cfg["d_model"] * cfg["d_ff"]
 
@@ -209,7 +220,7 @@ def run_reference(args):
     w2, b2 = rm.synthetic((f, d), 3, "weight").to(torch.bfloat16), rm.synthetic((d,), 4, "bias").to(torch.bfloat16)
     for _ in range(max(1, min(args.warmup, 2))):
         rm.ffn_forward(x, w1, b1, w2, b2, args.act)
-    steps = min(args.steps, 20)
+    steps = min(args.steps, 200)            # ~0.2 s per step on 16+ cores: the default 50 steps take ~10 s
     t0 = time.perf_counter()
     for _ in range(steps):
         rm.ffn_forward(x, w1, b1, w2, b2, args.act)
@@ -220,8 +231,7 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
             "warmup": args.warmup, "ms_per_step": el / steps * 1e3, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": "case4_gspmd_ff", "batch": cfg["batch"], "seq_len": cfg["seq"],
-                       "d_model": d, "d_ff": f, "activation": args.act, "bias": True},
+            "config": workload_config("case4_gspmd_ff", cfg, args.act, args.gpus),
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
                              "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
@@ -701,11 +711,10 @@ def main():
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16",
         "data": "synthetic",
-        "config": {"workload": args.workload, "batch": cfg["batch"], "seq_len": cfg["seq"], "d_model": cfg["d_model"],
-                   "d_ff": cfg["d_ff"], "activation": args.act, "bias": True, "parallelism": par_name,
-                   "api": "layers.FFNBench.step_resident -> b200_gemm_bf16_ex (C ABI) per shard",
-                   "l2": "inputs larger than L2 (x 134 MB, W1 134 MB, W2 134 MB, h 537 MB per step vs 126 MB L2)",
-                   "flops_per_step": total_flops},
+        "config": workload_config(args.workload, cfg, args.act, world),
+        "implementation": {"parallelism": par_name,
+                           "api": "layers.FFNBench.step_resident -> b200_gemm_bf16_ex (C ABI) per shard; the same step through "
+                                  "nn.jit(apply_fn) is the `api` object"},
         "clocks": clocks,
         "e2e": {"value": total_flops / (e2e_ms * 1e-3) / 1e12, "unit": UNIT, "ms_per_step": e2e_ms,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

@@ -24,6 +24,10 @@ def test_reference_arm_json_line():
     assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
     assert d["e2e"]["value"] == d["value"] > 0
     assert d["vs_baseline"] is None
+    # the config object is built by the same function in both arms: the driver's same-config comparison holds
+    sys.path.insert(0, ROOT)
+    import bench
+    assert d["config"] == bench.workload_config("case4_gspmd_ff", bench.WORKLOADS["case4_gspmd_ff"], "gelu_tanh", 1)
 
 
 def test_reference_arm_other_ranks_exit_quietly():
