@@ -152,6 +152,18 @@ typedef struct {
                                            time).  1: consecutive tiles cycle through the owner blocks, so every wave
                                            sends to all peers at once and the NVLink traffic is spread evenly over the
                                            kernel; same result, bit for bit */
+  /* Progress signals of a row-block scatter (all zero = off): the kernel produces its tiles raster group by raster group
+   * (tune.group_m row-blocks of 128 * tune.cta_group rows x all column-blocks); when every tile of group g is stored and
+   * visible system-wide it writes done_epoch into flag [done_sender * done_groups + g] of EVERY owner's flag array
+   * (done_flag_ptrs: device array of M / m_rows_per_block pointers into peer memory), so that b200_peer_progressive_sum
+   * on the owner reduces the rows of a group while the later groups are still being produced.  With m_block_interleave
+   * group g holds rows [g, g + 1) * (group_m / owners) * 128 * cta_group of every owner's block.  done_counters: local
+   * device array of done_groups uint32, zero-initialised once, never reset (it counts across launches).  Needs explicit
+   * tune.cta_group / block_n / group_m. */
+  unsigned int* done_counters;
+  unsigned int* const* done_flag_ptrs;
+  int done_sender, done_groups;
+  unsigned int done_epoch;
 } b200_gemm_args;
 int b200_gemm_bf16_ex(const b200_gemm_args* args, void* stream);
 
@@ -370,6 +382,13 @@ int b200_peer_gather(void* const* src_bases_dev, int world, int rank, int64_t sr
 int b200_peer_push(void* const* dst_bases_dev, int world, int rank, int64_t dst_off_bytes, const void* src, int64_t bytes,
                    int ctas, void* stream);
 int b200_peer_barrier(void* const* flag_ptrs_dev, int rank, int world, uint32_t epoch, void* stream);
+/* The local half of the fused reduce-scatter, running WHILE the pushing GEMMs still produce: for g = 0 .. groups-1 wait until
+ * flags[s * groups + g] >= epoch for every sender s (the progress signals of b200_gemm_args), then
+ * dst rows [g, g + 1) * rows_per_group = bf16(sum_s src[s * src_stride + those rows]) (+ bias).  `ctas` CTAs of 256 threads
+ * that co-reside with the persistent GEMM (no shared memory); enqueue it on a side stream before or beside the GEMM. */
+int b200_peer_progressive_sum(const uint32_t* flags, uint32_t epoch, int senders, int groups, int64_t rows_per_group,
+                              const void* src, int64_t src_stride, const void* bias, int64_t cols, void* dst, int ctas,
+                              void* stream);
 int b200_sum_bf16_partials(const void* src, int64_t src_stride, int nsrc, const void* bias, int64_t cols, void* dst,
                            int64_t n, void* stream);
 

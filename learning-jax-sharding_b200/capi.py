@@ -63,6 +63,7 @@ EXPORTED_SYMBOLS = (
     "b200_peer_copy2d",
     "b200_peer_gather",
     "b200_peer_push",
+    "b200_peer_progressive_sum",
     "b200_peer_barrier",
     "b200_sum_bf16_partials",
     "b200_random_fill",
@@ -98,7 +99,9 @@ class GemmArgs(ctypes.Structure):
                 ("out_dtype", ctypes.c_int), ("c_block_ptrs", ctypes.c_void_p), ("m_rows_per_block", ctypes.c_int),
                 ("m_block_rot", ctypes.c_int), ("M", ctypes.c_int), ("N", ctypes.c_int), ("K", ctypes.c_int),
                 ("epilogue", ctypes.c_int), ("a_layout", ctypes.c_int), ("tune", GemmTuning),
-                ("a_blocks_inner", ctypes.c_int), ("a_outer_stride", ctypes.c_int), ("m_block_interleave", ctypes.c_int)]
+                ("a_blocks_inner", ctypes.c_int), ("a_outer_stride", ctypes.c_int), ("m_block_interleave", ctypes.c_int),
+                ("done_counters", ctypes.c_void_p), ("done_flag_ptrs", ctypes.c_void_p), ("done_sender", ctypes.c_int),
+                ("done_groups", ctypes.c_int), ("done_epoch", ctypes.c_uint32)]
 
 
 class AttentionBwdArgs(ctypes.Structure):
@@ -141,6 +144,7 @@ def load():
     lib.b200_peer_free.argtypes = [vp]
     lib.b200_peer_copy2d.argtypes = [vp, i64, vp, i64, i64, i64, vp]
     lib.b200_peer_gather.argtypes = [vp, i32, i32, i64, i64, vp, i64, i32, i64, i32, vp]
+    lib.b200_peer_progressive_sum.argtypes = [vp, ctypes.c_uint32, i32, i32, i64, vp, i64, vp, i64, vp, i32, vp]
     lib.b200_peer_push.argtypes = [vp, i32, i32, i64, vp, i64, i32, vp]
     lib.b200_peer_barrier.argtypes = [vp, i32, i32, ctypes.c_uint32, vp]
     lib.b200_sum_bf16_partials.argtypes = [vp, i64, i32, vp, i64, vp, i64, vp]
@@ -502,7 +506,7 @@ def sum_partials_to_bf16(partials, bias=None, out=None):
 
 # ---------------------------------------------------------------- fused GEMM -> reduce-scatter plumbing
 def gemm_bf16_scatter(a, b, block_ptrs, rows_per_block: int, rot: int, ldc: int, *, b_layout=B_KN, a_block_stride: int = 0,
-                      M: int = 0, tune=None, a_view=None, interleave: bool = False):
+                      M: int = 0, tune=None, a_view=None, interleave: bool = False, progress=None):
     """a[M,K] @ b -> bf16 rows scattered to ``block_ptrs`` (a CUDA int64 tensor of M/rows_per_block base
     pointers, e.g. peer GPUs' receive slots): b200_gemm_bf16_ex with the row-block scatter.  With ``a_block_stride`` > 0
     block j of the product is read from rows [j * a_block_stride, j * a_block_stride + rows_per_block) of ``a`` (``M`` =
@@ -519,6 +523,10 @@ def gemm_bf16_scatter(a, b, block_ptrs, rows_per_block: int, rot: int, ldc: int,
     args.c_block_ptrs = block_ptrs.data_ptr()
     args.m_rows_per_block, args.m_block_rot = rows_per_block, rot
     args.m_block_interleave = int(bool(interleave))
+    if progress is not None:       # (counters tensor, owners' flag-array pointers tensor, sender index, groups, epoch)
+        counters, flag_ptrs, sender, groups, epoch = progress
+        args.done_counters, args.done_flag_ptrs = counters.data_ptr(), flag_ptrs.data_ptr()
+        args.done_sender, args.done_groups, args.done_epoch = int(sender), int(groups), int(epoch) & 0xFFFFFFFF
     if a_view is not None:      # two-level view: (rows_per_block, blocks_inner, inner_stride, outer_stride)
         args.a_rows_per_block, args.a_blocks_inner, args.a_block_stride, args.a_outer_stride = (int(v) for v in a_view)
     elif a_block_stride:
@@ -648,6 +656,18 @@ def peer_barrier(flag_ptrs, rank: int, world: int, epoch: int, stream=None):
     with torch.cuda.device(flag_ptrs.device):
         rc = load().b200_peer_barrier(_ptr(flag_ptrs), rank, world, epoch & 0xFFFFFFFF, st)
     _check(rc, "b200_peer_barrier")
+
+
+def peer_progressive_sum(flags_ptr: int, epoch: int, senders: int, groups: int, rows_per_group: int, src_ptr: int,
+                         src_stride: int, bias, cols: int, out, ctas: int, stream):
+    """b200_peer_progressive_sum: out rows of group g = bf16(sum over senders) (+ bias) as soon as every sender's progress
+    flag for g shows `epoch`; enqueued on ``stream`` to run beside the pushing GEMM."""
+    _require_cuda(bias, out)
+    with torch.cuda.device(out.device):
+        rc = load().b200_peer_progressive_sum(ctypes.c_void_p(flags_ptr), epoch & 0xFFFFFFFF, senders, groups, rows_per_group,
+                                              ctypes.c_void_p(src_ptr), src_stride, _ptr(bias), cols, _ptr(out), ctas,
+                                              ctypes.c_void_p(stream.cuda_stream))
+    _check(rc, "b200_peer_progressive_sum")
 
 
 def peer_push(dst_bases, world: int, rank: int, dst_off: int, src: torch.Tensor, ctas: int, stream):

@@ -65,6 +65,14 @@ struct GemmParams {
   // stores reach here whatever their shape, tools/diag/nvlink_store.cu; block after block, the 7/8 of the tiles that
   // are remote need more than that while they run and the link idles during the own block)
   int m_interleave;
+  // Progress signals of a row-block scatter (all null / 0 = off).  Tiles are produced raster group by raster group
+  // (group_m row-blocks x all column-blocks); once every tile of group g has been stored -- and made visible system-wide --
+  // the kernel writes `done_epoch` into flag [done_sender * done_groups + g] of EVERY owner's flag array, so that an owner
+  // can start reducing the rows of group g while this kernel is still producing the later groups.
+  unsigned int* done_counters;          // local, [done_groups], monotonic over launches (never reset)
+  unsigned int* const* done_flag_ptrs;  // device array [m_num_blocks] of the owners' flag arrays (peer memory)
+  int done_sender, done_groups;
+  unsigned int done_epoch;
   int num_stages;   // smem ring depth actually used (<= Cfg::kStages); tuning experiments only
   int a_mn_major;   // 1: A is stored [K, M] row-major (the transposed operand of a weight-gradient GEMM dW = X^T . dY):
                     // the A tile is loaded as two 64-row-wide MN-major chunks and the MMA reads it with the MN-major flag
@@ -404,6 +412,25 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         else mbar_arrive_cluster(&tmem_empty_bar[acc], 0);
       }
       if (++acc == Cfg::kAccStages) { acc = 0; acc_phase ^= 1; }
+      if (p.done_counters != nullptr) {
+        // this warp's stores of the tile are ordered before its count; the warp that completes the raster group publishes
+        __threadfence_system();
+        __syncwarp();
+        if (lane == 0) {
+          const int per_group = p.group_m * p.tiles_n;
+          const int g = tile / per_group;
+          const int rows_in_group = min(p.tiles_m - g * p.group_m, p.group_m);
+          const unsigned int target = static_cast<unsigned int>(rows_in_group * p.tiles_n * 4 * G);
+          unsigned int old;
+          asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(old) : "l"(p.done_counters + g) : "memory");
+          if ((old + 1) % target == 0) {
+            for (int o = 0; o < p.m_num_blocks; ++o) {
+              unsigned int* flag = p.done_flag_ptrs[o] + p.done_sender * p.done_groups + g;
+              asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(p.done_epoch) : "memory");
+            }
+          }
+        }
+      }
     }
   }
 
@@ -619,6 +646,17 @@ extern "C" int b200_gemm_bf16_ex(const b200_gemm_args* args, void* stream) {
   p.m_block_rot = args->m_block_rot;
   p.m_num_blocks = args->m_rows_per_block > 0 ? M / args->m_rows_per_block : 0;
   p.m_interleave = (args->m_block_interleave && args->m_rows_per_block > 0) ? 1 : 0;
+  if (args->done_counters != nullptr) {
+    B200_REQUIRE(args->m_rows_per_block > 0 && args->done_flag_ptrs != nullptr && args->done_groups > 0 &&
+                     args->done_sender >= 0 && args->tune.group_m > 0 && args->tune.cta_group > 0 && args->tune.block_n > 0,
+                 "b200_gemm_bf16: progress signals need the row-block scatter, the owners' flag arrays, and an explicit tile "
+                 "shape and raster group in `tune` (the caller sizes its groups from them)");
+    p.done_counters = args->done_counters;
+    p.done_flag_ptrs = args->done_flag_ptrs;
+    p.done_sender = args->done_sender;
+    p.done_groups = args->done_groups;
+    p.done_epoch = args->done_epoch;
+  }
   p.a_mn_major = a_km ? 1 : 0;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const bool kmajor = b_layout == B200_B_NK;

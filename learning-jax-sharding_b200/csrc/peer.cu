@@ -75,6 +75,67 @@ __global__ void __launch_bounds__(256) sum_bf16_partials_kernel(const __nv_bfloa
   }
 }
 
+// The reduction of sum_bf16_partials_kernel, one raster group of rows at a time, each as soon as every sender's progress flag for
+// that group shows this step's epoch (see GemmParams::done_*): runs beside the pushing GEMMs, so that only the last group's
+// share of the reduction is left when they finish.
+__global__ void __launch_bounds__(256) progressive_sum_kernel(const uint32_t* __restrict__ flags, uint32_t epoch, int senders,
+                                                             int groups, int64_t group_elems,
+                                                             const __nv_bfloat16* __restrict__ src, int64_t src_stride,
+                                                             const __nv_bfloat16* __restrict__ bias, int64_t cols,
+                                                             __nv_bfloat16* __restrict__ dst) {
+  const int64_t nvec = group_elems / 8;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int g = 0; g < groups; ++g) {
+    if (threadIdx.x < senders) {
+      const uint32_t* f = flags + threadIdx.x * groups + g;
+      const long long t0 = clock64();
+      uint32_t seen;
+      for (;;) {
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(f) : "memory");
+        if (static_cast<int32_t>(seen - epoch) >= 0) break;
+        __nanosleep(200);
+        if (clock64() - t0 > 8000000000ll) {   // ~4 s: a sender is missing -- fail instead of hanging the GPU
+          printf("b200: progressive sum timeout waiting for sender %d group %d epoch=%u seen=%u\n", (int)threadIdx.x, g, epoch, seen);
+          __trap();
+        }
+      }
+    }
+    __syncthreads();
+    const int64_t base = static_cast<int64_t>(g) * nvec;
+    for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+      float acc[8];
+#pragma unroll
+      for (int t = 0; t < 8; ++t) acc[t] = 0.f;
+      for (int r = 0; r < senders; ++r) {
+        const uint4 v = reinterpret_cast<const uint4*>(src + r * src_stride)[base + i];
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          const float2 f = __bfloat1622float2(h[t]);
+          acc[2 * t] += f.x;
+          acc[2 * t + 1] += f.y;
+        }
+      }
+      if (bias != nullptr) {
+        const uint4 bv = *reinterpret_cast<const uint4*>(bias + ((base + i) * 8) % cols);
+        const __nv_bfloat162* hb = reinterpret_cast<const __nv_bfloat162*>(&bv);
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          const float2 f = __bfloat1622float2(hb[t]);
+          acc[2 * t] = bf16_round(acc[2 * t]) + f.x;
+          acc[2 * t + 1] = bf16_round(acc[2 * t + 1]) + f.y;
+        }
+      }
+      uint4 o;
+      o.x = pack_bf16x2(acc[0], acc[1]);
+      o.y = pack_bf16x2(acc[2], acc[3]);
+      o.z = pack_bf16x2(acc[4], acc[5]);
+      o.w = pack_bf16x2(acc[6], acc[7]);
+      reinterpret_cast<uint4*>(dst)[base + i] = o;
+    }
+  }
+}
+
 // Pull one column chunk of every rank's weight shard into the local gathered matrix: W shards of
 // [rows, src_pitch] (this rank's own included), destination rows p*rows .. (p+1)*rows of a [W*rows, dst_pitch]
 // matrix.  16-byte loads straight from the peers' HBM over NVLink, eight in flight per thread; each CTA starts
@@ -248,6 +309,23 @@ extern "C" int b200_sum_bf16_partials(const void* src, int64_t src_stride, int n
   sum_bf16_partials_kernel<<<static_cast<int>(blocks), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<const __nv_bfloat16*>(src), src_stride, nsrc, reinterpret_cast<const __nv_bfloat16*>(bias),
       cols > 0 ? cols : 8, reinterpret_cast<__nv_bfloat16*>(dst), n);
+  B200_CUDA_CHECK(cudaGetLastError());
+  launch_counter().fetch_add(1);
+  return B200_OK;
+}
+
+extern "C" int b200_peer_progressive_sum(const uint32_t* flags, uint32_t epoch, int senders, int groups, int64_t rows_per_group,
+                                         const void* src, int64_t src_stride, const void* bias, int64_t cols, void* dst,
+                                         int ctas, void* stream) {
+  B200_REQUIRE(flags && src && dst && senders >= 1 && senders <= 64 && groups >= 1 && rows_per_group > 0 && cols > 0,
+               "b200_peer_progressive_sum: bad arguments (1..64 senders)");
+  B200_REQUIRE(cols % 8 == 0 && src_stride % 8 == 0, "b200_peer_progressive_sum: cols and src_stride must be multiples of 8");
+  B200_REQUIRE((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(bias)) % 16 == 0,
+               "b200_peer_progressive_sum: buffers must be 16-byte aligned");
+  B200_REQUIRE(ctas >= 1 && ctas <= 4096, "b200_peer_progressive_sum: ctas must be in [1, 4096]");
+  progressive_sum_kernel<<<ctas, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      flags, epoch, senders, groups, rows_per_group * cols, reinterpret_cast<const __nv_bfloat16*>(src), src_stride,
+      reinterpret_cast<const __nv_bfloat16*>(bias), cols, reinterpret_cast<__nv_bfloat16*>(dst));
   B200_CUDA_CHECK(cudaGetLastError());
   launch_counter().fetch_add(1);
   return B200_OK;

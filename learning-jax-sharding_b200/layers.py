@@ -127,7 +127,8 @@ class PeerReduceScatter:
     two-level row-blocked view (b200_gemm_args.a_blocks_inner); chunks then split the batch items.  `batch` = 1
     scatters contiguous blocks of the flattened rows."""
 
-    _FLAG_BYTES = 1024
+    _FLAG_BYTES = 16384        # [0, 1024): barrier flags; [1024, 16384): progress flags [sender][raster group]
+    _PROGRESS_OFF = 1024
 
     def __init__(self, T: int, N: int, group, device, chunks: int = 1, batch: int = 1):
         import torch.distributed as dist
@@ -173,7 +174,22 @@ class PeerReduceScatter:
             self.c_ptrs.append(per_chunk)
         self.buf = 0
         self.epoch = 0
-        self.side = torch.cuda.Stream(device=device) if self.chunks > 1 else None
+        # progressive form (B200_TP_PROGRESSIVE=1): the pushing GEMM signals every finished raster group (16 row-blocks of
+        # 256 rows, tiles cycling through the owners) to all owners, and the reduction runs group by group on a side stream
+        # WHILE the GEMM produces the later groups: only the last group's share of the sum is left after the last tile
+        self.progressive = (os.environ.get("B200_TP_PROGRESSIVE", "0") != "0" and self.chunks == 1 and 16 % W == 0
+                            and T % 4096 == 0 and N >= 256 and W * (T // 4096) * 4 <= self._FLAG_BYTES - self._PROGRESS_OFF)
+        if self.progressive:
+            self.groups = T // 4096                              # raster groups of the pushing GEMM
+            self.rows_per_group = (16 // W) * 256                # rows of every owner's block in one group
+            self.interleave = True
+            self.counters = torch.zeros(self.groups, dtype=torch.int32, device=device)
+            self.progress_ptrs = torch.tensor([b + self._PROGRESS_OFF for b in self.peer_base], dtype=torch.int64, device=device)
+            self.pepoch = 0
+            self.buf_free = [torch.cuda.Event() for _ in range(2)]
+            self.started = torch.cuda.Event()
+            self.sum_ctas = 2 * torch.cuda.get_device_properties(device).multi_processor_count
+        self.side = torch.cuda.Stream(device=device) if (self.chunks > 1 or self.progressive) else None
         self.pushed = [torch.cuda.Event() for _ in range(self.chunks)]
         self.reduced = torch.cuda.Event()
         dist.barrier(group=group)
@@ -209,6 +225,8 @@ class PeerReduceScatter:
         """out[T/W, N] = this rank's row block of sum over ranks of (a @ w) (+ bias): the partial product is stored into
         the owners' receive slots from the GEMM epilogue (NVLink), reduced locally after a flag barrier."""
         main = torch.cuda.current_stream(a.device)
+        if self.progressive:
+            return self._push_and_reduce_progressive(a, w, bias, out, main, record)
         for c in range(self.chunks):
             self._push(a, w, c)
             if record is not None:
@@ -228,6 +246,38 @@ class PeerReduceScatter:
                     record("reduce")
         if self.chunks > 1:
             main.wait_event(self.reduced)
+        self.buf ^= 1
+        return out
+
+    def _push_and_reduce_progressive(self, a, w, bias, out, main, record):
+        self.pepoch += 1
+        main.wait_event(self.buf_free[self.buf])     # every owner has finished reading this receive buffer (two steps ago)
+        self.started.record(main)
+        progress = (self.counters, self.progress_ptrs, self.rank, self.groups, self.pepoch)
+        tune = {"cta_group": 2, "block_n": 256, "group_m": 16}    # the reducer's groups are sized from this tile shape
+        rot = (self.rank + 1) % self.world
+        if self.batch > 1:
+            capi.gemm_bf16_scatter(a, w, self.c_ptrs[self.buf][0], self.R, rot, self.N, M=self.T,
+                                   a_view=(self.rpb, self.batch, self.seq, self.rpb), interleave=True, progress=progress, tune=tune)
+        else:
+            capi.gemm_bf16_scatter(a, w, self.c_ptrs[self.buf][0], self.R, rot, self.N, interleave=True, progress=progress,
+                                   tune=tune)
+        if record is not None:
+            record("gemm2")
+        # the reduction is enqueued AFTER the GEMM (whose persistent CTAs take their SMs first) on the side stream; its CTAs
+        # need no shared memory and fill in beside them, polling the progress flags
+        side = self.side
+        side.wait_event(self.started)                # `out` may be overwritten: everything before this step is done
+        src = self.base + self._FLAG_BYTES + (self.buf * self.world * self.slot) * 2
+        capi.peer_progressive_sum(self.base + self._PROGRESS_OFF, self.pepoch, self.world, self.groups, self.rows_per_group,
+                                  src, self.slot, bias, self.N, out, self.sum_ctas, side)
+        self.reduced.record(side)
+        self.epoch += 1
+        capi.peer_barrier(self.flag_ptrs, self.rank, self.world, self.epoch, stream=side)   # off the step's critical path
+        self.buf_free[self.buf].record(side)
+        main.wait_event(self.reduced)
+        if record is not None:
+            record("reduce")
         self.buf ^= 1
         return out
 

@@ -65,6 +65,26 @@ def main():
     print(f"[rank {rank}] fused TP chunks=1 vs chunks={fused.rs.chunks}: {'identical' if good else 'DIFFERENT'}", flush=True)
     ok &= good
     del fused1
+    # progressive form: per-raster-group progress flags from the pushing GEMM, reduction beside it on a side stream
+    os.environ["B200_TP_PROGRESSIVE"] = "1"
+    Tp = 2 * T                                         # two raster groups of 4096 rows
+    xp = torch.cat([x, rm.synthetic((T, d), 50)])
+    wantp = rm.ffn_forward(xp, w1, b1, w2, b2, "gelu_tanh").float()
+    for batch in (1, 4):
+        fp = layers.FusedTensorParallelFFN(bf(w1[:, rank * fl:(rank + 1) * fl].contiguous()), bf(b1[rank * fl:(rank + 1) * fl]),
+                                           bf(w2[rank * fl:(rank + 1) * fl].contiguous()), bf(b2), "gelu_tanh", Tp,
+                                           dist.group.WORLD, batch=batch)
+        for it in range(5):
+            yp = fp.forward(bf(xp))
+        torch.cuda.synchronize()
+        ref = wantp[fp.rs.global_rows(torch.arange(Tp // world), rank)]
+        err = (yp.cpu().float() - ref).abs()
+        good = bool((err <= 2e-2 * ref.abs() + 2e-2).all()) and fp.rs.progressive
+        print(f"[rank {rank}] fused TP, progressive reduction ({fp.rs.groups} groups, batch={batch}): max_abs={err.max().item():.3e} "
+              f"{'OK' if good else 'FAIL'}", flush=True)
+        ok &= good
+        del fp
+    os.environ["B200_TP_PROGRESSIVE"] = "0"
     # scatter along seq of a [batch, seq] activation (two-level A view): [4, T/4/W, d] per rank, chunks over batch items
     fused_s = layers.FusedTensorParallelFFN(bf(w1[:, rank * fl:(rank + 1) * fl].contiguous()), bf(b1[rank * fl:(rank + 1) * fl]),
                                             bf(w2[rank * fl:(rank + 1) * fl].contiguous()), bf(b2), "gelu_tanh", T,
