@@ -462,6 +462,45 @@ def test_gemm_scatter_two_level_view_and_interleave(ljs):
             assert torch.equal(slots2[j], slots[j])
 
 
+def test_gemm_progress_signals_and_progressive_sum(ljs):
+    """The pushing GEMM's per-raster-group progress flags (b200_gemm_args.done_*) and the reduction that follows them
+    (b200_peer_progressive_sum), with the 'owners' being local buffers: two senders' partial products of 8192 rows (two
+    raster groups), four owners, interleaved tile order; flags and counters end at their expected values, and two steps in a
+    row (counters are never reset) give the sum of the partials."""
+    capi = ljs.capi
+    M, N, K, W, S = 8192, 512, 256, 4, 2
+    R = M // W
+    groups, rows_per_group = M // 4096, (16 // W) * 256
+    w = rm.synthetic((K, N), 131, "weight").to(torch.bfloat16)
+    bias = rm.synthetic((N,), 132, "bias").to(torch.bfloat16)
+    a = [rm.synthetic((M, K), 133 + s).to(torch.bfloat16) for s in range(S)]
+    flags = torch.zeros((W, S, groups), dtype=torch.int32, device="cuda")            # one flag array per owner
+    flag_ptrs = torch.tensor([flags[o].data_ptr() for o in range(W)], dtype=torch.int64, device="cuda")
+    counters = [torch.zeros(groups, dtype=torch.int32, device="cuda") for _ in range(S)]
+    slots = torch.zeros((W, S, R, N), dtype=torch.bfloat16, device="cuda")           # owner o, sender s
+    side = torch.cuda.Stream()
+    tune = {"cta_group": 2, "block_n": 256, "group_m": 16}
+    for epoch in (1, 2):
+        outs = [torch.full((R, N), float("nan"), dtype=torch.bfloat16, device="cuda") for _ in range(W)]
+        side.wait_stream(torch.cuda.current_stream())
+        for o in range(W):      # the owners' reductions are queued first here and wait for the flags
+            capi.peer_progressive_sum(flags[o].data_ptr(), epoch, S, groups, rows_per_group, slots[o].data_ptr(), R * N,
+                                      _dev(bias), N, outs[o], 8, side)
+        for s in range(S):
+            ptrs = torch.tensor([slots[o, s].data_ptr() for o in range(W)], dtype=torch.int64, device="cuda")
+            capi.gemm_bf16_scatter(_dev(a[s]), _dev(w), ptrs, R, (s + 1) % W, N, interleave=True, tune=tune,
+                                   progress=(counters[s], flag_ptrs, s, groups, epoch))
+        torch.cuda.synchronize()
+        assert (flags == epoch).all()
+        tiles_n, per_tile = N // 256, 4 * 2
+        for s in range(S):
+            assert counters[s].tolist() == [epoch * 16 * tiles_n * per_tile] * groups
+        parts = [rm.dense_bf16(a[s], w).float() for s in range(S)]
+        want = (sum(parts).to(torch.bfloat16).float() + bias.float()).to(torch.bfloat16).float()
+        for o in range(W):
+            torch.testing.assert_close(outs[o].cpu().float(), want[o * R:(o + 1) * R], rtol=1e-2, atol=1e-2)
+
+
 @pytest.mark.parametrize("causal", [False, True])
 def test_sharded_mha_layer_one_gpu(ljs, causal):
     """layers.ShardedMHA (fused qkv projection -> attention on strided views -> out projection) against the
