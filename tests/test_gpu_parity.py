@@ -482,14 +482,18 @@ def test_gemm_progress_signals_and_progressive_sum(ljs):
     tune = {"cta_group": 2, "block_n": 256, "group_m": 16}
     for epoch in (1, 2):
         outs = [torch.full((R, N), float("nan"), dtype=torch.bfloat16, device="cuda") for _ in range(W)]
+        ad, wd, bd = [_dev(t) for t in a], _dev(w), _dev(bias)
+        ptrs = [torch.tensor([slots[o, s].data_ptr() for o in range(W)], dtype=torch.int64, device="cuda") for s in range(S)]
+        torch.cuda.synchronize()
         side.wait_stream(torch.cuda.current_stream())
-        for o in range(W):      # the owners' reductions are queued first here and wait for the flags
-            capi.peer_progressive_sum(flags[o].data_ptr(), epoch, S, groups, rows_per_group, slots[o].data_ptr(), R * N,
-                                      _dev(bias), N, outs[o], 8, side)
+        # as in the product: the pushing GEMMs are enqueued first (their persistent CTAs take the SMs), the reductions after
+        # them on a side stream, where they poll the flags beside the GEMMs
         for s in range(S):
-            ptrs = torch.tensor([slots[o, s].data_ptr() for o in range(W)], dtype=torch.int64, device="cuda")
-            capi.gemm_bf16_scatter(_dev(a[s]), _dev(w), ptrs, R, (s + 1) % W, N, interleave=True, tune=tune,
+            capi.gemm_bf16_scatter(ad[s], wd, ptrs[s], R, (s + 1) % W, N, interleave=True, tune=tune,
                                    progress=(counters[s], flag_ptrs, s, groups, epoch))
+        for o in range(W):
+            capi.peer_progressive_sum(flags[o].data_ptr(), epoch, S, groups, rows_per_group, slots[o].data_ptr(), R * N,
+                                      bd, N, outs[o], 8, side)
         torch.cuda.synchronize()
         assert (flags == epoch).all()
         tiles_n, per_tile = N // 256, 4 * 2
