@@ -10,6 +10,10 @@ from oracle import reference_math as rm
 rt = ljs.init_distributed("nccl")
 import torch.distributed as dist
 rank, world, dev = rt.rank, rt.world, rt.torch_device
+os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+_log = open(os.path.join(ROOT, "gpurun_out", f"prog_rank{rank}.log"), "w")
+def print(*a, **k):      # noqa: A001 - per-rank log file: survives a device trap
+    _log.write(" ".join(str(x) for x in a) + "\n"); _log.flush(); os.fsync(_log.fileno())
 T, d, f = 8192, 1024, 4096
 x = rm.synthetic((T, d), 0)
 w1, b1 = rm.synthetic((d, f), 1, "weight"), rm.synthetic((f,), 2, "bias")
@@ -23,8 +27,12 @@ for batch in (1, 4):
     print(f"[rank {rank}] batch={batch} progressive={fp.rs.progressive} groups={getattr(fp.rs, 'groups', None)}", flush=True)
     xd = bf(x)
     for it in range(4):
+        print(f"[rank {rank}] step {it} enqueue")
         y = fp.forward(xd)
+        print(f"[rank {rank}] step {it} enqueued; epoch={fp.rs.pepoch} buf={fp.rs.buf}")
         torch.cuda.synchronize()
+        fl_local = torch.as_tensor(layers._RawCudaBuffer(fp.rs.base + 1024, 64), device=dev).view(torch.int32)
+        print(f"[rank {rank}] flags={fl_local[:8].tolist()}")
         print(f"[rank {rank}] batch={batch} step {it} done; counters={fp.rs.counters.tolist()}", flush=True)
     ref = want[fp.rs.global_rows(torch.arange(T // world), rank)]
     err = (y.cpu().float() - ref).abs()
