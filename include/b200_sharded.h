@@ -385,7 +385,9 @@ int b200_peer_barrier(void* const* flag_ptrs_dev, int rank, int world, uint32_t 
 /* The local half of the fused reduce-scatter, running WHILE the pushing GEMMs still produce: for g = 0 .. groups-1 wait until
  * flags[s * groups + g] >= epoch for every sender s (the progress signals of b200_gemm_args), then
  * dst rows [g, g + 1) * rows_per_group = bf16(sum_s src[s * src_stride + those rows]) (+ bias).  `ctas` CTAs of 256 threads
- * that co-reside with the persistent GEMM (no shared memory); enqueue it on a side stream before or beside the GEMM. */
+ * that co-reside with the persistent GEMM (no shared memory).  Enqueue it on the SAME stream RIGHT AFTER the pushing
+ * b200_gemm_bf16_ex: it is launched as a programmatic dependent of the kernel before it, i.e. it starts once that whole grid
+ * is resident and runs beside it (starting earlier could starve a GEMM CTA of its SM and deadlock on that CTA's tiles). */
 int b200_peer_progressive_sum(const uint32_t* flags, uint32_t epoch, int senders, int groups, int64_t rows_per_group,
                               const void* src, int64_t src_stride, const void* bias, int64_t cols, void* dst, int ctas,
                               void* stream);

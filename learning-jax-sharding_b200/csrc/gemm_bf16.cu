@@ -176,6 +176,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   }
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  // Programmatic dependent launch: a kernel enqueued behind this one with the programmatic-serialization attribute (the
+  // progressive reduction, b200_peer_progressive_sum) may start once EVERY CTA of this grid has got here -- i.e. once the
+  // whole persistent grid is resident, so that the dependent's CTAs can only fill in beside it, never take an SM a CTA of
+  // this grid still needs.  Without such a dependent the instruction does nothing.
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
   if (warp == 0) {
     // ===================== TMA producer (whole warp in the loop, one elected lane issues) =====================

@@ -323,10 +323,25 @@ extern "C" int b200_peer_progressive_sum(const uint32_t* flags, uint32_t epoch, 
   B200_REQUIRE((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(bias)) % 16 == 0,
                "b200_peer_progressive_sum: buffers must be 16-byte aligned");
   B200_REQUIRE(ctas >= 1 && ctas <= 4096, "b200_peer_progressive_sum: ctas must be in [1, 4096]");
-  progressive_sum_kernel<<<ctas, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      flags, epoch, senders, groups, rows_per_group * cols, reinterpret_cast<const __nv_bfloat16*>(src), src_stride,
-      reinterpret_cast<const __nv_bfloat16*>(bias), cols, reinterpret_cast<__nv_bfloat16*>(dst));
-  B200_CUDA_CHECK(cudaGetLastError());
+  // Launched as a PROGRAMMATIC DEPENDENT of the kernel before it on the stream (the pushing GEMM): it starts when every CTA
+  // of that grid has executed griddepcontrol.launch_dependents -- all of the persistent GEMM is resident by then -- and runs
+  // beside it.  (Started any earlier, its CTAs could take the registers or thread slots of an SM that a GEMM CTA still needs,
+  // and then wait for ever for the tiles of that very CTA.)  It never executes griddepcontrol.wait: the data it reads is
+  // ordered by the per-group flags, not by the GEMM's completion.
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(ctas);
+  cfg.blockDim = dim3(256);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = reinterpret_cast<cudaStream_t>(stream);
+  cudaLaunchAttribute attrs[1];
+  attrs[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attrs[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attrs;
+  cfg.numAttrs = 1;
+  const int64_t group_elems = rows_per_group * cols;
+  B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, progressive_sum_kernel, flags, epoch, senders, groups, group_elems,
+                                     reinterpret_cast<const __nv_bfloat16*>(src), src_stride,
+                                     reinterpret_cast<const __nv_bfloat16*>(bias), cols, reinterpret_cast<__nv_bfloat16*>(dst)));
   launch_counter().fetch_add(1);
   return B200_OK;
 }

@@ -252,7 +252,6 @@ class PeerReduceScatter:
     def _push_and_reduce_progressive(self, a, w, bias, out, main, record):
         self.pepoch += 1
         main.wait_event(self.buf_free[self.buf])     # every owner has finished reading this receive buffer (two steps ago)
-        self.started.record(main)
         progress = (self.counters, self.progress_ptrs, self.rank, self.groups, self.pepoch)
         tune = {"cta_group": 2, "block_n": 256, "group_m": 16}    # the reducer's groups are sized from this tile shape
         rot = (self.rank + 1) % self.world
@@ -262,22 +261,19 @@ class PeerReduceScatter:
         else:
             capi.gemm_bf16_scatter(a, w, self.c_ptrs[self.buf][0], self.R, rot, self.N, interleave=True, progress=progress,
                                    tune=tune)
-        if record is not None:
-            record("gemm2")
-        # the reduction is enqueued AFTER the GEMM (whose persistent CTAs take their SMs first) on the side stream; its CTAs
-        # need no shared memory and fill in beside them, polling the progress flags
-        side = self.side
-        side.wait_event(self.started)                # `out` may be overwritten: everything before this step is done
+        # the reduction follows the GEMM on the SAME stream as its programmatic dependent: it starts once the whole persistent
+        # grid is resident, fills in beside it (no shared memory) and polls the progress flags group by group
         src = self.base + self._FLAG_BYTES + (self.buf * self.world * self.slot) * 2
         capi.peer_progressive_sum(self.base + self._PROGRESS_OFF, self.pepoch, self.world, self.groups, self.rows_per_group,
-                                  src, self.slot, bias, self.N, out, self.sum_ctas, side)
-        self.reduced.record(side)
+                                  src, self.slot, bias, self.N, out, self.sum_ctas, main)
+        if record is not None:
+            record("gemm2")                          # (the GEMM and the reduction beside it: they end together)
+        self.reduced.record(main)
+        side = self.side
+        side.wait_event(self.reduced)
         self.epoch += 1
         capi.peer_barrier(self.flag_ptrs, self.rank, self.world, self.epoch, stream=side)   # off the step's critical path
         self.buf_free[self.buf].record(side)
-        main.wait_event(self.reduced)
-        if record is not None:
-            record("reduce")
         self.buf ^= 1
         return out
 

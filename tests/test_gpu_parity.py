@@ -478,22 +478,21 @@ def test_gemm_progress_signals_and_progressive_sum(ljs):
     flag_ptrs = torch.tensor([flags[o].data_ptr() for o in range(W)], dtype=torch.int64, device="cuda")
     counters = [torch.zeros(groups, dtype=torch.int32, device="cuda") for _ in range(S)]
     slots = torch.zeros((W, S, R, N), dtype=torch.bfloat16, device="cuda")           # owner o, sender s
-    side = torch.cuda.Stream()
     tune = {"cta_group": 2, "block_n": 256, "group_m": 16}
     for epoch in (1, 2):
         outs = [torch.full((R, N), float("nan"), dtype=torch.bfloat16, device="cuda") for _ in range(W)]
         ad, wd, bd = [_dev(t) for t in a], _dev(w), _dev(bias)
         ptrs = [torch.tensor([slots[o, s].data_ptr() for o in range(W)], dtype=torch.int64, device="cuda") for s in range(S)]
         torch.cuda.synchronize()
-        side.wait_stream(torch.cuda.current_stream())
-        # as in the product: the pushing GEMMs are enqueued first (their persistent CTAs take the SMs), the reductions after
-        # them on a side stream, where they poll the flags beside the GEMMs
+        main = torch.cuda.current_stream()
+        # as in the product: sender 0's GEMM first, then -- behind the LAST pushing GEMM on the same stream, as its
+        # programmatic dependent -- the owners' reductions, which poll the flags beside it
         for s in range(S):
             capi.gemm_bf16_scatter(ad[s], wd, ptrs[s], R, (s + 1) % W, N, interleave=True, tune=tune,
                                    progress=(counters[s], flag_ptrs, s, groups, epoch))
         for o in range(W):
             capi.peer_progressive_sum(flags[o].data_ptr(), epoch, S, groups, rows_per_group, slots[o].data_ptr(), R * N,
-                                      bd, N, outs[o], 8, side)
+                                      bd, N, outs[o], 8, main)
         torch.cuda.synchronize()
         assert (flags == epoch).all()
         tiles_n, per_tile = N // 256, 4 * 2
