@@ -188,7 +188,8 @@ class PeerReduceScatter:
             self.pepoch = 0
             self.buf_free = [torch.cuda.Event() for _ in range(2)]
             self.started = torch.cuda.Event()
-            self.sum_ctas = 2 * torch.cuda.get_device_properties(device).multi_processor_count
+            self.sum_ctas = int(os.environ.get("B200_TP_SUM_CTAS", "0")) or \
+                2 * torch.cuda.get_device_properties(device).multi_processor_count
         self.side = torch.cuda.Stream(device=device) if (self.chunks > 1 or self.progressive) else None
         self.pushed = [torch.cuda.Event() for _ in range(self.chunks)]
         self.reduced = torch.cuda.Event()
