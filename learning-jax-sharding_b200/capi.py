@@ -16,7 +16,8 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200sl.so")
+# B200_LIB_PATH selects another build of the same library (A/B runs of compile-time variants, tools/build_variants.sh)
+LIB_PATH = os.environ.get("B200_LIB_PATH") or os.path.join(_HERE, "libb200sl.so")
 
 # enums of include/b200_sharded.h
 BF16, F32 = 0, 1

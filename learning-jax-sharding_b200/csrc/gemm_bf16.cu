@@ -17,6 +17,10 @@
 #include "host_common.h"
 #include "sm100_ptx.cuh"
 
+#ifndef B200_PROGRESS_FENCE
+#define B200_PROGRESS_FENCE 1   // fence between a warp's tile stores and its progress count: 1 = fence.acq_rel.sys, 2 = fence.sc.sys
+#endif                          // (0 = none: timing experiments only, the flags are then not ordered after the data)
+
 namespace b200 {
 
 constexpr int kBM = 128;        // rows of C per CTA (TMEM lanes)
@@ -419,7 +423,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       if (++acc == Cfg::kAccStages) { acc = 0; acc_phase ^= 1; }
       if (p.done_counters != nullptr) {
         // this warp's stores of the tile are ordered before its count; the warp that completes the raster group publishes
-        __threadfence_system();
+#if B200_PROGRESS_FENCE == 2
+        __threadfence_system();                                        // fence.sc.sys
+#elif B200_PROGRESS_FENCE == 1
+        asm volatile("fence.acq_rel.sys;" ::: "memory");
+#endif
         __syncwarp();
         if (lane == 0) {
           const int per_group = p.group_m * p.tiles_n;
