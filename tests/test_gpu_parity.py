@@ -495,9 +495,9 @@ def test_gemm_progress_signals_and_progressive_sum(ljs):
                                       bd, N, outs[o], 8, main)
         torch.cuda.synchronize()
         assert (flags == epoch).all()
-        tiles_n, per_tile = N // 256, 4 * 2
+        tiles_n = N // 256
         for s in range(S):
-            assert counters[s].tolist() == [epoch * 16 * tiles_n * per_tile] * groups
+            assert counters[s].tolist() == [epoch * 16 * tiles_n * 2] * groups       # (tile, CTA of the pair) per group
         parts = [rm.dense_bf16(a[s], w).float() for s in range(S)]
         want = (sum(parts).to(torch.bfloat16).float() + bias.float()).to(torch.bfloat16).float()
         for o in range(W):
