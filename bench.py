@@ -204,6 +204,32 @@ def cpu_ffn_sample(cfg, seconds=12.0, tokens=2048, act="gelu_tanh"):
             "seconds": el, "ms_per_pass": el / reps * 1e3}
 
 
+def cpu_attention_sample(cfg, seq=1024, seconds=10.0):
+    """The oracle's MHA forward (projections + attention core + out-projection) on the host cores on a bounded sample of the
+    workload: ONE batch item cut to `seq` tokens, same widths and heads (attention cost is quadratic in the sequence, so the
+    sample's own FLOPs are what the rate is computed from)."""
+    from oracle import reference_math as rm
+    torch.set_num_threads(os.cpu_count() or 1)
+    M, H, D = cfg["d_model"], cfg["heads"], cfg["dim_head"]
+    x = rm.synthetic((1, seq, M), 0)
+    params = {"to_q": rm.synthetic((M, H * D), 1, "weight"), "to_k": rm.synthetic((M, H * D), 2, "weight"),
+              "to_v": rm.synthetic((M, H * D), 3, "weight"),
+              "to_out_0": (rm.synthetic((H * D, M), 4, "weight"), rm.synthetic((M,), 5, "bias"))}
+    rm.mha_forward(x[:, :128], params, H, D, cfg["causal"])
+    reps, t0 = 0, time.perf_counter()
+    while True:
+        rm.mha_forward(x, params, H, D, cfg["causal"])
+        reps += 1
+        el = time.perf_counter() - t0
+        if el >= seconds or reps >= 50:
+            break
+    core = 2.0 * H * seq * (seq + 1) * D if cfg["causal"] else 4.0 * H * seq * seq * D
+    flops = (core + 8.0 * seq * M * H * D) * reps
+    return {"value": flops / el / 1e12, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"oracle mha_forward on 1 batch item x {seq} of {cfg['seq']} tokens (same widths, {H} heads x {D}), {reps} "
+                      f"passes in {el:.1f} s; rate from the sample's own FLOPs; JAX is not installable here"}
+
+
 def run_reference(args):
     """--impl reference: the reference's own CPU path is jax/XLA:CPU, which cannot be installed in this
     image; the timed stand-in is the oracle port on all host cores, each step a bounded sample."""
@@ -649,7 +675,7 @@ def main():
 
     if args.workload in ATTN_WORKLOADS:
         return layers.bench_attention(args, ATTN_WORKLOADS[args.workload], rank, world, dev, METRIC, UNIT,
-                                      peaks, ClockSampler(local_rank), attn_flops)
+                                      peaks, ClockSampler(local_rank), attn_flops, cpu_sample=cpu_attention_sample)
     cfg = WORKLOADS[args.workload]
     bench = layers.FFNBench(cfg, args.act, rank, world, dev, chunks=args.chunks)
     total_flops = ffn_flops(cfg)

@@ -1055,13 +1055,56 @@ def attention_core_sample(dev, B, S, H, D, causal, peaks, iters=5):
     return {"shape": [B, S, H, D], "causal": causal, "ms": ms, "core_tflops": tf, "core_frac_of_peak": tf / peaks["bf16_burst"]}
 
 
-def bench_attention(args, cfg, rank, world, dev, metric, unit, peaks, sampler, attn_flops):
+def _attention_e2e(r, dev, world, steps=3):
+    """The same layer with x in pinned HOST memory and y returned to pinned host memory, every step (no pipelining across
+    steps: upload, forward, download).  Returns (ms per step max over ranks, h2d bytes, d2h bytes) summed over ranks."""
+    layer, x = r["layer"], r["x"]
+    x_host = x.cpu().pin_memory()
+    y0 = layer.forward(x)
+    y_host = torch.empty(y0.shape, dtype=y0.dtype).pin_memory()
+    x_dev = torch.empty_like(x)
+
+    def step():
+        x_dev.copy_(x_host, non_blocking=True)
+        y = layer.forward(x_dev)
+        y_host.copy_(y, non_blocking=True)
+
+    step()
+    torch.cuda.synchronize(dev)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1) / steps
+    h2d, d2h = x_host.numel() * 2, y_host.numel() * 2
+    if dist is not None:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+        b = torch.tensor([h2d, d2h], device=dev, dtype=torch.float64)
+        dist.all_reduce(b)
+        h2d, d2h = int(b[0]), int(b[1])
+    return ms, h2d, d2h
+
+
+def bench_attention(args, cfg, rank, world, dev, metric, unit, peaks, sampler, attn_flops, cpu_sample=None):
     """`bench.py --workload case5_attention_dense|case6_attention`: the full MHA layer at the config shape."""
     sampler.start()
-    r = run_attention_workload(cfg, rank, world, dev, args.steps, args.warmup)
+    r = run_attention_workload(cfg, rank, world, dev, args.steps, args.warmup, keep=True)
     clocks = sampler.stop()
+    e2e_ms, h2d, d2h = _attention_e2e(r, dev, world)
     if rank != 0:
         return
+    total0 = r["core_flops"] + r["proj_flops"]
+    e2e = {"value": total0 / (e2e_ms * 1e-3) / 1e12, "unit": unit, "ms_per_step": e2e_ms, "h2d_bytes_per_step": h2d,
+           "d2h_bytes_per_step": d2h, "what": "x uploaded from pinned host memory and y downloaded every step, not pipelined"}
+    cpu = cpu_sample(cfg) if (cpu_sample is not None and world == 1 and not args.no_cpu_baseline) else None
     total = r["core_flops"] + r["proj_flops"]
     val = total / (r["ms_per_step"] * 1e-3) / 1e12
     core_tf = r["core_flops"] / (r["parts_ms"]["attn"] * 1e-3) / 1e12 / world
@@ -1079,4 +1122,4 @@ def bench_attention(args, cfg, rank, world, dev, metric, unit, peaks, sampler, a
         "roofline": {"bound": "tensor", "kernel": "attention_fwd9_kernel (CTA pairs; per GPU, attention core only)",
                      "achieved": core_tf, "peak": peaks["bf16_burst"], "unit": unit,
                      "frac": core_tf / peaks["bf16_burst"], "peak_source": peaks["source"], "traffic": None},
-        "cpu_baseline": None, "e2e": None}), flush=True)
+        "cpu_baseline": cpu, "e2e": e2e}), flush=True)
