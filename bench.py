@@ -573,19 +573,6 @@ def case1a_leg(ljs, dist, dev, rank, world):
     out["large_fp32"] = {"shape": [n, n, n], "ms": ms, "tflops": 2.0 * n ** 3 / (ms * 1e-3) / 1e12,
                          "kernel": "gemm_f32_kernel (FFMA, no TF32)",
                          "parity_ok": bool(torch.allclose(c32[idx].cpu().double(), ref, rtol=1e-5, atol=1e-5 * n ** 0.5))}
-    # the same product on the tensor cores: three-term bf16 splits of both operands (re-done every call) + one bf16 GEMM
-    for _ in range(2):
-        ljs.capi.gemm_f32_tensor_core(a32, b32, out=c32)
-    e0.record()
-    for _ in range(5):
-        ljs.capi.gemm_f32_tensor_core(a32, b32, out=c32)
-    e1.record()
-    torch.cuda.synchronize(dev)
-    ms = e0.elapsed_time(e1) / 5
-    out["large_fp32_tensor_core"] = {"shape": [n, n, n], "ms": ms, "tflops": 2.0 * n ** 3 / (ms * 1e-3) / 1e12,
-                                     "kernel": "b200_split_f32_to_bf16x3 (both operands, every call) + gemm_bf16_kernel over K' = 6 K, "
-                                               "f32 accumulation: what lax.dot uses for large f32 shards",
-                                     "parity_ok": bool(torch.allclose(c32[idx].cpu().double(), ref, rtol=1e-5, atol=1e-5 * n ** 0.5))}
     out["all_parity_ok"] = all(v.get("parity_ok", True) for v in out.values() if isinstance(v, dict)) and \
         all(l["parity_ok"] for l in out.get("literal_2x4", {}).get("layouts", {}).values())
     return out

@@ -181,19 +181,6 @@ int b200_gemm_f32(const float* A, int64_t lda, int64_t strideA, const float* B, 
                   void* stream);
 
 /*
- * fp32 matmul on the tensor cores, for shapes where the FFMA kernel above is the bottleneck.  An f32 number is the sum of
- * three bf16 terms up to 2^-24 of its size; b200_split_f32_to_bf16x3 writes the terms of an operand as the operand of ONE
- * bf16 GEMM with a six times longer contraction dim --
- *   as_a != 0: src [rows, cols] -> dst [rows, 6 cols], column blocks (a1 a1 a2 a1 a2 a3)
- *   as_a == 0: src [rows, cols] -> dst [6 rows, cols], row blocks    (b1 b2 b1 b3 b2 b1)
- * -- so that b200_gemm_bf16(A', B', out_dtype = B200_F32, K = 6 K) accumulates the six products a_i b_j with i + j <= 4 in
- * f32: every bf16 x bf16 product is exact in f32 and the dropped terms are ~2^-24 |a||b|, so the result meets the rtol 1e-5
- * of the sharded jax.lax.dot cases (case1a.py:49 and siblings) at about a sixth of the bf16 rate instead of FFMA speed.
- * cols and ld_src multiples of 4.
- */
-int b200_split_f32_to_bf16x3(const float* src, int64_t ld_src, void* dst, int64_t rows, int64_t cols, int as_a, void* stream);
-
-/*
  * Multi-head attention core, forward:  O = softmax(scale * Q.K^T [+ causal mask]) . V
  * Q: [B,Sq,H,D], K,V: [B,Sk,H,D], O: [B,Sq,H,D]; bf16; head dim innermost, heads
  * second-innermost (the reference's "b s n h" layout, so the (b,S,N*D) projection

@@ -34,7 +34,6 @@ EXPORTED_SYMBOLS = (
     "b200_gemm_bf16_rowblocked",
     "b200_gemm_bf16_ex",
     "b200_gemm_f32",
-    "b200_split_f32_to_bf16x3",
     "b200_attention_fwd",
     "b200_attention_fwd_ex",
     "b200_ffn_fwd",
@@ -151,7 +150,6 @@ def load():
     lib.b200_peer_barrier.argtypes = [vp, i32, i32, ctypes.c_uint32, vp]
     lib.b200_sum_bf16_partials.argtypes = [vp, i64, i32, vp, i64, vp, i64, vp]
     lib.b200_gemm_f32.argtypes = [vp, i64, i64, vp, i64, i64, vp, i64, i64, i32, i32, i32, i32, i32, vp]
-    lib.b200_split_f32_to_bf16x3.argtypes = [vp, i64, vp, i64, i64, i32, vp]
     lib.b200_attention_fwd.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32] + [i64] * 12 + [f32, i32, vp]
     lib.b200_random_fill.argtypes = [ctypes.POINTER(RandomArgs), vp, vp]
     lib.b200_attention_fwd_ex.argtypes = [ctypes.POINTER(AttentionArgs), vp]
@@ -358,30 +356,6 @@ def gemm_f32(a, b, *, out=None, accumulate=False):
             o3.stride(0), Bt, M, N, K, int(bool(accumulate)), _stream(a))
     _check(rc, "b200_gemm_f32")
     return out
-
-
-def gemm_f32_tensor_core(a, b, *, out=None):
-    """a [M,K] @ b [K,N] in fp32 accuracy on the tensor cores: both operands split into three bf16 terms
-    (b200_split_f32_to_bf16x3) and ONE bf16 GEMM over a six times longer contraction dim with f32 accumulation.  For large
-    shapes (the FFMA kernel of gemm_f32 is the right tool for the literal 4x16 sizes); K and N multiples of 8."""
-    _require_cuda(a, b, out)
-    if a.dtype != torch.float32 or b.dtype != torch.float32 or a.dim() != 2 or b.dim() != 2 or a.shape[1] != b.shape[0]:
-        raise B200Error("gemm_f32_tensor_core takes 2-D fp32 operands that contract")
-    if a.stride(1) != 1 or b.stride(1) != 1:
-        raise B200Error("gemm_f32_tensor_core takes operands with a contiguous last dim")
-    M, K = a.shape
-    N = b.shape[1]
-    if K % 8 or N % 8 or a.stride(0) % 4 or b.stride(0) % 4:
-        raise B200Error("gemm_f32_tensor_core: K and N must be multiples of 8 (row strides multiples of 4)")
-    a6 = torch.empty((M, 6 * K), dtype=torch.bfloat16, device=a.device)
-    b6 = torch.empty((6 * K, N), dtype=torch.bfloat16, device=a.device)
-    with torch.cuda.device(a.device):
-        lib = load()
-        _check(lib.b200_split_f32_to_bf16x3(_ptr(a), a.stride(0), _ptr(a6), M, K, 1, _stream(a)), "b200_split_f32_to_bf16x3")
-        _check(lib.b200_split_f32_to_bf16x3(_ptr(b), b.stride(0), _ptr(b6), K, N, 0, _stream(a)), "b200_split_f32_to_bf16x3")
-    if out is None:
-        out = torch.empty((M, N), dtype=torch.float32, device=a.device)
-    return gemm_bf16(a6, b6, out=out)
 
 
 def attention_fwd(q, k, v, *, scale=None, causal=False, out=None, lse=None, variant=0):

@@ -135,52 +135,6 @@ __global__ void __launch_bounds__(256) attention_combine_kernel(float* __restric
   }
 }
 
-
-// fp32 -> three bf16 terms (x = x1 + x2 + x3 up to 2^-24 |x|: x1 = bf16(x), x2 = bf16(x - x1), x3 = bf16(x - x1 - x2)),
-// written as the operand of ONE bf16 tensor-core GEMM that reproduces the fp32 product: with the contraction dim six times
-// as long and the term blocks ordered  A' = [a1 a1 a2 a1 a2 a3],  B' = [b1; b2; b1; b3; b2; b1],  A'.B' sums the six
-// products a_i b_j with i + j <= 4 in the f32 accumulator (every bf16 x bf16 product is exact in f32; what is dropped,
-// a2 b3 + a3 b2 + a3 b3, is ~2^-24 |a||b|, the size of fp32's own rounding).
-//   as_a != 0: src [rows, cols] -> dst [rows, 6 cols], column blocks (1,1,2,1,2,3)     (the A operand, K = cols)
-//   as_a == 0: src [rows, cols] -> dst [6 rows, cols], row blocks (1,2,1,3,2,1)        (the B operand, K = rows)
-__global__ void __launch_bounds__(256) split_bf16x3_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst,
-                                                          int64_t rows, int64_t cols, int64_t ld_src, int as_a) {
-  const int64_t n4 = rows * (cols / 4);
-  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
-  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += stride) {
-    const int64_t r = i / (cols / 4), c = (i % (cols / 4)) * 4;
-    const float4 x = *reinterpret_cast<const float4*>(src + r * ld_src + c);
-    const float xs[4] = {x.x, x.y, x.z, x.w};
-    uint32_t t[3][2];
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      float v1[2], v2[2], v3[2];
-#pragma unroll
-      for (int e = 0; e < 2; ++e) {
-        const float v = xs[2 * h + e];
-        v1[e] = bf16_round(v);
-        const float r1 = v - v1[e];
-        v2[e] = bf16_round(r1);
-        v3[e] = bf16_round(r1 - v2[e]);
-      }
-      t[0][h] = pack_bf16x2(v1[0], v1[1]);
-      t[1][h] = pack_bf16x2(v2[0], v2[1]);
-      t[2][h] = pack_bf16x2(v3[0], v3[1]);
-    }
-    if (as_a) {
-      const int blk[6] = {0, 0, 1, 0, 1, 2};
-      __nv_bfloat16* d = dst + r * (6 * cols) + c;
-#pragma unroll
-      for (int b = 0; b < 6; ++b) *reinterpret_cast<uint2*>(d + b * cols) = make_uint2(t[blk[b]][0], t[blk[b]][1]);
-    } else {
-      const int blk[6] = {0, 1, 0, 2, 1, 0};
-#pragma unroll
-      for (int b = 0; b < 6; ++b)
-        *reinterpret_cast<uint2*>(dst + (b * rows + r) * cols + c) = make_uint2(t[blk[b]][0], t[blk[b]][1]);
-    }
-  }
-}
-
 }  // namespace b200
 
 using namespace b200;
@@ -243,19 +197,6 @@ extern "C" int b200_attention_combine(float* acc, float* lse_acc, const void* o_
   else
     attention_combine_kernel<64><<<static_cast<int>(blocks), 256, 0, st>>>(acc, lse_acc, reinterpret_cast<const __nv_bfloat16*>(o_blk),
                                                                         lse_blk, rows, S, H, first);
-  B200_CUDA_CHECK(cudaGetLastError());
-  launch_counter().fetch_add(1);
-  return B200_OK;
-}
-
-extern "C" int b200_split_f32_to_bf16x3(const float* src, int64_t ld_src, void* dst, int64_t rows, int64_t cols, int as_a,
-                                        void* stream) {
-  B200_REQUIRE(src && dst && rows > 0 && cols > 0 && ld_src >= cols, "b200_split_f32_to_bf16x3: bad arguments");
-  B200_REQUIRE(cols % 4 == 0 && ld_src % 4 == 0, "b200_split_f32_to_bf16x3: cols and ld_src must be multiples of 4");
-  B200_REQUIRE(reinterpret_cast<uintptr_t>(src) % 16 == 0 && reinterpret_cast<uintptr_t>(dst) % 8 == 0,
-               "b200_split_f32_to_bf16x3: src must be 16-byte aligned, dst 8-byte aligned");
-  split_bf16x3_kernel<<<grid_for(rows * (cols / 4)), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      src, reinterpret_cast<__nv_bfloat16*>(dst), rows, cols, ld_src, as_a);
   B200_CUDA_CHECK(cudaGetLastError());
   launch_counter().fetch_add(1);
   return B200_OK;

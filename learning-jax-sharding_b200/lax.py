@@ -33,12 +33,6 @@ def _key(sl):
 def _local_matmul(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
     comp = _rt.local_compute()
     if a.dtype == torch.float32:
-        # large shards: fp32 accuracy from three-term bf16 splits on the tensor cores; the literal shapes stay on the FFMA kernel
-        M, K = a.shape
-        N = b.shape[1]
-        if M * N * K >= (1 << 27) and K % 8 == 0 and N % 8 == 0 and hasattr(comp, "gemm_f32_tensor_core") and a.is_cuda \
-                and a.stride(1) == 1 and b.stride(1) == 1 and a.stride(0) % 4 == 0 and b.stride(0) % 4 == 0:
-            return comp.gemm_f32_tensor_core(a, b)
         return comp.gemm_f32(a, b)
     if a.dtype == torch.bfloat16:
         return comp.gemm_bf16(a, b)

@@ -83,30 +83,6 @@ def test_gemm_f32_shapes(ljs, shape):
     torch.testing.assert_close(got2.double(), want + c0.double(), rtol=1e-5, atol=1e-5 * K ** 0.5)
 
 
-@pytest.mark.parametrize("shape", [(512, 512, 512), (1000, 264, 136), (2048, 1024, 4096)])
-def test_gemm_f32_on_tensor_cores(ljs, shape):
-    """fp32 product from three-term bf16 splits (b200_split_f32_to_bf16x3 + one bf16 GEMM with f32 accumulation): the same
-    rtol 1e-5 bar as the FFMA kernel, against f64; the split itself is exact to 2^-24."""
-    capi = ljs.capi
-    M, N, K = shape
-    a, b = rm.synthetic((M, K), 5), rm.synthetic((K, N), 6)
-    got = capi.gemm_f32_tensor_core(_dev(a), _dev(b)).cpu()
-    want = a.double() @ b.double()
-    torch.testing.assert_close(got.double(), want, rtol=1e-5, atol=1e-5 * K ** 0.5)
-    ffma = capi.gemm_f32(_dev(a), _dev(b)).cpu()
-    assert (got.double() - want).abs().max() <= 4 * (ffma.double() - want).abs().max() + 1e-6     # same league as true fp32
-    # the terms: a1 + a2 + a3 reproduces a to 2^-24 relative
-    a6 = torch.empty((M, 6 * K), dtype=torch.bfloat16, device="cuda")
-    ad = _dev(a)
-    rc = capi.load().b200_split_f32_to_bf16x3(ad.data_ptr(), K, a6.data_ptr(), M, K, 1, None)
-    assert rc == 0
-    torch.cuda.synchronize()
-    t = a6.cpu().double().reshape(M, 6, K)
-    assert torch.equal(t[:, 0], t[:, 1]) and torch.equal(t[:, 0], t[:, 3]) and torch.equal(t[:, 2], t[:, 4])
-    rec = t[:, 0] + t[:, 2] + t[:, 5]
-    assert ((rec - a.double()).abs() <= 2.0 ** -23 * a.double().abs() + 1e-38).all()
-
-
 # ------------------------------------------------------------------------------ bf16 GEMM
 @pytest.mark.parametrize("g,bn", [(0, 0), (1, 256), (1, 128), (1, 64), (2, 256), (2, 128)])
 @pytest.mark.parametrize("layout", ["kn", "nk"])
