@@ -270,12 +270,11 @@ class PeerReduceScatter:
         if record is not None:
             record("gemm2")                          # (the GEMM and the reduction beside it: they end together)
         self.reduced.record(main)
-        if os.environ.get("B200_TP_PROG_DIAG", "") != "nobarrier":
-            side = self.side
-            side.wait_event(self.reduced)
-            self.epoch += 1
-            capi.peer_barrier(self.flag_ptrs, self.rank, self.world, self.epoch, stream=side)   # off the step's critical path
-            self.buf_free[self.buf].record(side)
+        side = self.side
+        side.wait_event(self.reduced)
+        self.epoch += 1
+        capi.peer_barrier(self.flag_ptrs, self.rank, self.world, self.epoch, stream=side)   # off the step's critical path
+        self.buf_free[self.buf].record(side)
         self.buf ^= 1
         return out
 
