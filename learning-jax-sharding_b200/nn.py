@@ -113,6 +113,30 @@ def _to_bf16(t: torch.Tensor) -> torch.Tensor:
     return _rt.local_compute().cast_f32_to_bf16(t)
 
 
+def _param_bf16(p: ShardedArray) -> ShardedArray:
+    """The bf16 image of an f32 PARAMETER array, shard by shard, made once and kept on the shard tensors themselves (flax casts
+    its f32 parameters on every nn.Dense call; a resident layer need not).  Casting BEFORE any resharding also halves the bytes
+    an FSDP-style weight gather moves.  `invalidate_param_casts` drops the copies of parameters that were updated in place
+    (TrainState.apply_gradients calls it)."""
+    if p.dtype == torch.bfloat16:
+        return p
+    shards = {}
+    for d, t in p.local_shards.items():
+        c = t.__dict__.get("_b200_bf16")
+        if c is None:
+            c = _to_bf16(t)
+            t.__dict__["_b200_bf16"] = c
+        shards[d] = c
+    return ShardedArray(p.shape, torch.bfloat16, p.sharding, shards)
+
+
+def invalidate_param_casts(*params):
+    for p in params:
+        if isinstance(p, ShardedArray):
+            for t in p.local_shards.values():
+                t.__dict__.pop("_b200_bf16", None)
+
+
 # ------------------------------------------------------------------------------- Dense
 def dense(x: ShardedArray, kernel: ShardedArray, bias: Optional[ShardedArray] = None, *, epilogue: str = "none",
           scatter_dim: Optional[int] = None) -> ShardedArray:
@@ -130,6 +154,9 @@ def dense(x: ShardedArray, kernel: ShardedArray, bias: Optional[ShardedArray] = 
     rt = _rt.get_runtime()
     comp = _rt.local_compute()
     mesh = x.sharding.mesh
+    kernel = _param_bf16(kernel)                  # cast once per parameter (and before any gather: half the bytes)
+    if bias is not None:
+        bias = _param_bf16(bias)
     xa = _axes(x)
     kw, nw = _axes(kernel)
     rows, kx = xa[:-1], xa[-1]
@@ -161,8 +188,8 @@ def dense(x: ShardedArray, kernel: ShardedArray, bias: Optional[ShardedArray] = 
         xs = x.shard(d)
         lead = xs.shape[:-1]
         x2 = _to_bf16(xs.reshape(-1, xs.shape[-1]))
-        w = _to_bf16(kernel.shard(d))
-        b = _to_bf16(bias.shard(d)) if bias is not None else None
+        w = kernel.shard(d)
+        b = bias.shard(d) if bias is not None else None
         if reduce_axes:
             y2 = comp.gemm_bf16(x2, w, out_dtype=torch.float32)          # raw f32 partials
         else:

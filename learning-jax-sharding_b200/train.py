@@ -74,6 +74,7 @@ class TrainState:
                                    step=step, lr=self.tx.learning_rate, b1=self.tx.b1, b2=self.tx.b2, eps=self.tx.eps)
         from . import nn as _nn
         _nn.invalidate_fast_layers()      # the fused layers hold bf16 copies of the f32 parameters just updated in place
+        _nn.invalidate_param_casts(*self.params.values())     # ... and so do the parameter arrays themselves
         return TrainState(step, self.apply_fn, self.params, self.tx, self.mu, self.nu)
 
 
