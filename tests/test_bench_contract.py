@@ -43,3 +43,16 @@ def test_product_arm_needs_a_gpu():
                          capture_output=True, text=True, timeout=300, cwd=ROOT)
     assert out.returncode != 0
     assert "no CPU fallback" in (out.stderr + out.stdout)
+
+
+def test_bench_parity_bound_is_the_tests_bound():
+    """bench.py restates the tolerance of tests/_tol.py (so that it needs nothing from tests/ at run time): same number."""
+    sys.path.insert(0, ROOT)
+    import bench
+    from tests import _tol
+    g = torch.Generator().manual_seed(0)
+    want = torch.randn(64, 128, generator=g) * 0.05
+    got = want + torch.randn(64, 128, generator=g) * 2e-4
+    need, ulps, max_abs = bench._scaled_need(got, want)
+    assert abs(need - _tol.scaled_error(got, want, 2e-2)) < 1e-9
+    assert max_abs == float((got.double() - want.double()).abs().max()) and ulps > 0
